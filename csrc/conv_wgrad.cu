@@ -1,0 +1,299 @@
+// Filter-gradient ("wgrad") convolution for sm_100a on tcgen05/TMEM.
+//
+//   dW[k, r, s, c] += sum_{m in pixel range} dY[m, k] * X[pixel(m) + (r,s), c]
+//
+// GEMM view: M' = Cout (128 rows per CTA), N' = a slab of Cin (<= 256), K' = output pixels.
+// Both operands are "MN-major" for the tensor core - the reduction index (pixel) is the slow
+// axis in memory - which tcgen05.mma supports natively for 16-bit types, so neither tensor is
+// transposed in memory:
+//   A' = dY  tile, tiled TMA box   [64 pixels][<=64 out-channels], swizzled
+//   B' = X   tile, im2col TMA box  [64 pixels][<=64 in-channels] of ONE filter tap, swizzled,
+//        zero-filled at the image border, honouring the forward stride.
+// Work is split over (tap, Cout tile, Cin slab, pixel range); every CTA reduces its pixel range
+// into TMEM and adds the fp32 tile into dW with vector red.global (split-K).
+//
+// Replaces cudnnConvolutionBackwardFilter in the reference's autodiff graph (op K3).
+#include "common.cuh"
+#include "host.cuh"
+#include "../include/drn_b200.h"
+
+namespace drn {
+namespace {
+
+constexpr int kPix = 64;          // pixels (GEMM-K) per pipeline stage
+constexpr int kThreads = 192;     // warp0 TMA, warp1 MMA (+TMEM alloc), warps 2-5 epilogue
+constexpr int kMaxStages = 8;
+
+struct WgradParams {
+  int chunks_total;     // ceil(M / 64)
+  int chunks_per_split;
+  int splits;
+  int co_tiles, ci_tiles, taps;
+  int S;
+  int PQ, Q;
+  int stride, pad;
+  int Kout, C;
+  long long dw_row_stride;  // R*S*C
+  float* dw;
+};
+
+template <int CWA, int CWB, int NB>
+struct WCfg {
+  static constexpr int kRBA = CWA * 2, kRBB = CWB * 2;
+  static constexpr int kABoxes = 128 / CWA, kBBoxes = NB / CWB;
+  static constexpr int kABoxBytes = kPix * kRBA, kBBoxBytes = kPix * kRBB;
+  static constexpr int kABytes = kABoxes * kABoxBytes;  // 16 KB
+  static constexpr int kBBytesRaw = kBBoxes * kBBoxBytes;
+  static constexpr int kBBytes = (kBBytesRaw + 1023) / 1024 * 1024;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagesRaw = (200 * 1024) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > kMaxStages ? kMaxStages : kStagesRaw;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 1024;
+  static constexpr int kTmemCols = NB <= 32 ? 32 : NB <= 64 ? 64 : NB <= 128 ? 128 : 256;
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
+               "f"(d)
+               : "memory");
+}
+
+template <int CWA, int CWB, int NB>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_constant__ CUtensorMap tmapX,
+                  const WgradParams p) {
+  using C_ = WCfg<CWA, CWB, NB>;
+  constexpr int kStages = C_::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t sStages = smem_base;
+  const uint32_t sBar = sStages + kStages * C_::kStageBytes;
+  auto full_bar = [&](int s) { return sBar + 8u * s; };
+  auto empty_bar = [&](int s) { return sBar + 8u * (kMaxStages + s); };
+  const uint32_t tfull_bar = sBar + 8u * (2 * kMaxStages);
+  const uint32_t sTmemPtr = sBar + 8u * (2 * kMaxStages + 1);
+  volatile uint32_t* tmem_ptr_gen =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + (sTmemPtr - smem_base));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // decode the work unit
+  int u = blockIdx.x;
+  const int split = u % p.splits;
+  u /= p.splits;
+  const int ci_tile = u % p.ci_tiles;
+  u /= p.ci_tiles;
+  const int co_tile = u % p.co_tiles;
+  const int tap = u / p.co_tiles;
+  const int r = tap / p.S;
+  const int s = tap - r * p.S;
+  const int chunk_begin = split * p.chunks_per_split;
+  int chunk_end = chunk_begin + p.chunks_per_split;
+  if (chunk_end > p.chunks_total) chunk_end = p.chunks_total;
+  const int n_chunks = chunk_end - chunk_begin;  // may be <= 0 for trailing splits
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmapDY);
+    tma_prefetch_desc(&tmapX);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(full_bar(i), 1);
+      mbar_init(empty_bar(i), 1);
+    }
+    mbar_init(tfull_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(sTmemPtr, C_::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_gen;
+
+  if (n_chunks > 0) {
+    if (warp == 0) {
+      if (elect_one()) {
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int ch = chunk_begin; ch < chunk_end; ++ch) {
+          const int m0 = ch * kPix;
+          const int img = m0 / p.PQ;
+          const int rem = m0 - img * p.PQ;
+          const int op = rem / p.Q;
+          const int oq = rem - op * p.Q;
+          mbar_wait(empty_bar(stage), phase ^ 1, 0x110 + stage);
+          const uint32_t a_dst = sStages + stage * C_::kStageBytes;
+          const uint32_t b_dst = a_dst + C_::kABytes;
+          mbar_arrive_expect_tx(full_bar(stage), C_::kABytes + C_::kBBytesRaw);
+#pragma unroll
+          for (int i = 0; i < C_::kABoxes; ++i)
+            tma_load_2d(a_dst + i * C_::kABoxBytes, &tmapDY, full_bar(stage),
+                        co_tile * 128 + i * CWA, m0);
+#pragma unroll
+          for (int i = 0; i < C_::kBBoxes; ++i)
+            tma_load_im2col_4d(b_dst + i * C_::kBBoxBytes, &tmapX, full_bar(stage),
+                               ci_tile * NB + i * CWB, oq * p.stride - p.pad,
+                               op * p.stride - p.pad, img, static_cast<uint16_t>(s),
+                               static_cast<uint16_t>(r));
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    } else if (warp == 1) {
+      if (elect_one()) {
+        constexpr uint32_t kIdesc = make_idesc_bf16(128, NB, 1, 1);
+        constexpr uint32_t kLayA = umma_layout_for_swizzle_bytes(C_::kRBA);
+        constexpr uint32_t kLayB = umma_layout_for_swizzle_bytes(C_::kRBB);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int ch = 0; ch < n_chunks; ++ch) {
+          mbar_wait(full_bar(stage), phase, 0x120 + stage);
+          tc_fence_after();
+          const uint32_t a_addr = sStages + stage * C_::kStageBytes;
+          const uint32_t b_addr = a_addr + C_::kABytes;
+#pragma unroll
+          for (int kk = 0; kk < kPix / 16; ++kk) {
+            // MN-major: 16 reduction rows further down = 16 * row_bytes; LBO = distance between
+            // MN atoms (one TMA box), SBO = distance between 8-row groups.
+            const uint64_t a_desc = make_smem_desc(a_addr + kk * 16 * C_::kRBA, C_::kABoxBytes,
+                                                   8 * C_::kRBA, kLayA);
+            const uint64_t b_desc = make_smem_desc(b_addr + kk * 16 * C_::kRBB, C_::kBBoxBytes,
+                                                   8 * C_::kRBB, kLayB);
+            umma_f16(tmem_base, a_desc, b_desc, kIdesc, (ch | kk) != 0 ? 1u : 0u);
+          }
+          umma_commit(empty_bar(stage));
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(tfull_bar);
+      }
+    } else {
+      // epilogue: warps 2..5 -> TMEM lane quadrants 2,3,0,1
+      const int quad = warp & 3;
+      const int row = quad * 32 + lane;
+      const int co = co_tile * 128 + row;
+      mbar_wait(tfull_bar, 0, 0x140);
+      tc_fence_after();
+      float* dst_row = p.dw + (long long)co * p.dw_row_stride + (long long)tap * p.C + ci_tile * NB;
+      constexpr int kStep = NB >= 32 ? 32 : 16;
+#pragma unroll 1
+      for (int c0 = 0; c0 < NB; c0 += kStep) {
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + c0;
+        if constexpr (kStep == 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr, v);
+          tmem_ld_wait();
+          if (co < p.Kout) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4)
+              red_add_v4(dst_row + c0 + i, __uint_as_float(v[i]), __uint_as_float(v[i + 1]),
+                         __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+          }
+        } else {
+          uint32_t v[16];
+          tmem_ld_32x16(taddr, v);
+          tmem_ld_wait();
+          if (co < p.Kout) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 4)
+              red_add_v4(dst_row + c0 + i, __uint_as_float(v[i]), __uint_as_float(v[i + 1]),
+                         __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C_::kTmemCols);
+  }
+}
+
+template <int CWA, int CWB, int NB>
+int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* dw, int split_k,
+                 cudaStream_t stream) {
+  using C_ = WCfg<CWA, CWB, NB>;
+  const long long M = 1LL * d.N * d.P * d.Q;
+  WgradParams p;
+  p.chunks_total = (int)((M + kPix - 1) / kPix);
+  p.co_tiles = (d.K + 127) / 128;
+  p.ci_tiles = d.C / NB;
+  p.taps = d.R * d.S;
+  const int units = p.taps * p.co_tiles * p.ci_tiles;
+  int splits = split_k;
+  if (splits <= 0) {
+    // ~2 waves of CTAs, but keep at least 8 chunks (512 pixels) per CTA
+    splits = (2 * num_sms() + units - 1) / units;
+    int max_splits = p.chunks_total / 8;
+    if (max_splits < 1) max_splits = 1;
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+  }
+  if (splits > p.chunks_total) splits = p.chunks_total;
+  p.splits = splits;
+  p.chunks_per_split = (p.chunks_total + splits - 1) / splits;
+  p.S = d.S;
+  p.PQ = d.P * d.Q;
+  p.Q = d.Q;
+  p.stride = d.stride;
+  p.pad = d.pad_lo;
+  p.Kout = d.K;
+  p.C = d.C;
+  p.dw_row_stride = 1LL * d.R * d.S * d.C;
+  p.dw = dw;
+
+  CUtensorMap tDY, tX;
+  if (int e = tmap_tiled_2d(&tDY, dy, 2, (uint64_t)M, d.K, d.K, kPix, CWA, C_::kRBA)) return e;
+  if (int e = tmap_im2col_nhwc(&tX, x, d.N, d.H, d.W, d.C, -d.pad_lo, -d.pad_lo,
+                               d.pad_hi - (d.R - 1), d.pad_hi - (d.S - 1), d.stride, d.stride, CWB,
+                               kPix, C_::kRBB))
+    return e;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<CWA, CWB, NB>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        C_::kSmemBytes));
+    attr_set = true;
+  }
+  const int grid = units * splits;
+  conv_wgrad_kernel<CWA, CWB, NB><<<grid, kThreads, C_::kSmemBytes, stream>>>(tDY, tX, p);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int CWA>
+int dispatch_b(const drn_conv_desc& d, const void* x, const void* dy, float* dw, int split_k,
+               cudaStream_t st) {
+  if (d.C == 16) return launch_wgrad<CWA, 16, 16>(d, x, dy, dw, split_k, st);
+  if (d.C == 32) return launch_wgrad<CWA, 32, 32>(d, x, dy, dw, split_k, st);
+  if (d.C % 256 == 0) return launch_wgrad<CWA, 64, 256>(d, x, dy, dw, split_k, st);
+  if (d.C % 128 == 0) return launch_wgrad<CWA, 64, 128>(d, x, dy, dw, split_k, st);
+  return launch_wgrad<CWA, 64, 64>(d, x, dy, dw, split_k, st);
+}
+
+}  // namespace
+}  // namespace drn
+
+extern "C" int drn_conv_wgrad(const drn_conv_desc* desc, const void* x, const void* dy, float* dw,
+                              int split_k, void* stream) {
+  using namespace drn;
+  const drn_conv_desc& d = *desc;
+  DRN_REQUIRE(d.C == 16 || d.C == 32 || d.C % 64 == 0,
+              "conv_wgrad: C must be 16, 32 or a multiple of 64 (got %d)", d.C);
+  DRN_REQUIRE(d.K % 16 == 0, "conv_wgrad: K must be a multiple of 16 (got %d)", d.K);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (d.K == 16) return dispatch_b<16>(d, x, dy, dw, split_k, st);
+  if (d.K == 32) return dispatch_b<32>(d, x, dy, dw, split_k, st);
+  DRN_REQUIRE(d.K % 64 == 0, "conv_wgrad: K must be 16, 32 or a multiple of 64 (got %d)", d.K);
+  return dispatch_b<64>(d, x, dy, dw, split_k, st);
+}

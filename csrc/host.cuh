@@ -1,0 +1,50 @@
+// Host-side plumbing shared by the C-ABI launchers: error reporting, the driver
+// entry points for tensor-map encoding (resolved at run time so the library links
+// without libcuda), and a small cache of encoded CUtensorMaps.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <unordered_map>
+
+namespace drn {
+
+// Last error text, per thread; returned by drn_last_error().
+std::string& last_error();
+int fail(const char* fmt, ...);
+
+#define DRN_CHECK_CUDA(expr)                                                              \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess)                                                                \
+      return ::drn::fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                         __LINE__);                                                       \
+  } while (0)
+
+#define DRN_REQUIRE(cond, ...)                  \
+  do {                                          \
+    if (!(cond)) return ::drn::fail(__VA_ARGS__); \
+  } while (0)
+
+int num_sms();
+
+enum SwizzleMode { SWZ_NONE = 0, SWZ_32 = 32, SWZ_64 = 64, SWZ_128 = 128 };
+
+// 2-D tiled map over a row-major [rows][cols] matrix of 2- or 4-byte elements.
+// `row_stride_elems` is the distance between rows (>= cols).
+int tmap_tiled_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols,
+                  uint64_t row_stride_elems, uint32_t box_rows, uint32_t box_cols, int swizzle_bytes);
+
+// im2col map over an NHWC bf16 tensor. Corners follow the CUDA driver convention:
+// lower = -pad_lo, upper = pad_hi - (filter - 1) (dilation 1).
+int tmap_im2col_nhwc(CUtensorMap* out, const void* base, int N, int H, int W, int C, int lower_h,
+                     int lower_w, int upper_h, int upper_w, int stride_h, int stride_w,
+                     uint32_t channels_per_pixel, uint32_t pixels_per_column, int swizzle_bytes);
+
+}  // namespace drn

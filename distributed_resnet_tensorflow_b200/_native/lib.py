@@ -1,0 +1,94 @@
+"""ctypes binding of libdrn_b200.so (C ABI in include/drn_b200.h).
+
+The library is built in-tree by ``_native/build.py``. On a machine with a GPU the ops in
+``distributed_resnet_tensorflow_b200.ops`` REQUIRE it: there is no silent PyTorch fallback on
+CUDA tensors - a missing library raises ``NativeLibraryError``.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "libdrn_b200.so"
+
+
+class NativeLibraryError(RuntimeError):
+    pass
+
+
+class ConvDesc(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int) for n in
+                ("N", "H", "W", "C", "K", "R", "S", "stride", "pad_lo", "pad_hi", "P", "Q")]
+
+
+EPI_PLAIN, EPI_RESADD, EPI_BNBWD = 0, 1, 2
+
+_lib = None
+
+_vp = ctypes.c_void_p
+_i = ctypes.c_int
+_f = ctypes.c_float
+_ll = ctypes.c_longlong
+
+# name -> (restype, argtypes)
+_SIGNATURES = {
+    "drn_last_error": (ctypes.c_char_p, []),
+    "drn_watchdog_status": (_i, []),
+    "drn_num_sms": (_i, []),
+    "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
+    "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
+}
+
+
+def register(name: str, restype, argtypes) -> None:
+    """Declare one more C function (used by the op modules next to their wrappers)."""
+    _SIGNATURES[name] = (restype, argtypes)
+    if _lib is not None and hasattr(_lib, name):
+        fn = getattr(_lib, name)
+        fn.restype, fn.argtypes = restype, argtypes
+
+
+def load(build_if_missing: bool = True):
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        if not build_if_missing or os.environ.get("DRN_NO_BUILD"):
+            raise NativeLibraryError(f"{LIB_PATH} not found; run python -m "
+                                     "distributed_resnet_tensorflow_b200._native.build")
+        from . import build as _build
+        _build.build()
+    try:
+        lib = ctypes.CDLL(str(LIB_PATH))
+    except OSError as e:  # pragma: no cover
+        raise NativeLibraryError(f"cannot load {LIB_PATH}: {e}") from e
+    for name, (restype, argtypes) in _SIGNATURES.items():
+        if hasattr(lib, name):
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = restype, argtypes
+    _lib = lib
+    return lib
+
+
+def available() -> bool:
+    try:
+        load(build_if_missing=False)
+        return True
+    except NativeLibraryError:
+        return False
+
+
+def check(status: int, what: str = "") -> None:
+    if status != 0:
+        msg = load().drn_last_error().decode(errors="replace")
+        raise RuntimeError(f"libdrn_b200 {what} failed: {msg}")
+
+
+def call(name: str, *args) -> None:
+    lib = load()
+    fn = getattr(lib, name, None)
+    if fn is None:
+        raise NativeLibraryError(f"symbol {name} missing from {LIB_PATH} (stale build?)")
+    check(fn(*args), name)
