@@ -1,0 +1,361 @@
+// BatchNorm (+ReLU) kernels around the convolution epilogues. NHWC bf16 activations, fp32 statistics.
+//
+// Forward (training):  the producing convolution accumulates per-channel sum / sum-of-squares
+//   (conv_igemm.cu) -> drn_bn_finalize turns them into (scale, shift), saves (mean, invstd) and
+//   updates the moving averages -> drn_bn_apply writes a = relu(y*scale + shift).
+// Backward:  dm = da * [a > 0] and the reductions s1 = sum dm, s2 = sum dm*y come from the dgrad
+//   epilogue (or drn_bn_bwd_mask_reduce) -> drn_bn_bwd_finalize emits dgamma/dbeta and the three
+//   per-channel coefficients of  dy = A*dm + B*y + C  -> drn_bn_bwd_apply (+ optional addend,
+//   the identity-shortcut gradient).
+//
+// Numerics follow tf.layers.batch_normalization(fused=True) as used by the reference
+// (resnet_model_official.py:41-50): biased variance to normalise, unbiased variance into the
+// moving average, decay 0.997, eps 1e-5.  Ops K5-K9.
+#include "common.cuh"
+#include "host.cuh"
+#include "../include/drn_b200.h"
+
+namespace drn {
+namespace {
+
+constexpr int kThreads = 256;
+
+struct alignas(16) BF8 {
+  uint32_t v[4];
+};
+__device__ __forceinline__ void unpack8(const BF8& p, float (&f)[8]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = bf16lo(p.v[i]);
+    f[2 * i + 1] = bf16hi(p.v[i]);
+  }
+}
+__device__ __forceinline__ BF8 pack8(const float (&f)[8]) {
+  BF8 p;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) p.v[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
+  return p;
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void bn_finalize_kernel(const float* __restrict__ stats, int stats_ld, float inv_count,
+                                   float unbias, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* __restrict__ run_mean,
+                                   float* __restrict__ run_var, float one_minus_decay, float eps,
+                                   float2* __restrict__ scale_shift, float2* __restrict__ mean_invstd,
+                                   int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float mean = stats[c] * inv_count;
+  float var = fmaf(-mean, mean, stats[stats_ld + c] * inv_count);
+  var = fmaxf(var, 0.f);
+  const float invstd = rsqrtf(var + eps);
+  const float sc = gamma[c] * invstd;
+  scale_shift[c] = make_float2(sc, fmaf(-mean, sc, beta[c]));
+  mean_invstd[c] = make_float2(mean, invstd);
+  if (run_mean != nullptr) {
+    // moving -= (moving - batch) * (1 - decay)   (assign_moving_average, zero_debias=False)
+    run_mean[c] -= (run_mean[c] - mean) * one_minus_decay;
+    run_var[c] -= (run_var[c] - var * unbias) * one_minus_decay;
+  }
+}
+
+__global__ void bn_inference_params_kernel(const float* __restrict__ gamma,
+                                           const float* __restrict__ beta,
+                                           const float* __restrict__ run_mean,
+                                           const float* __restrict__ run_var, float eps,
+                                           float2* __restrict__ scale_shift, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float sc = gamma[c] * rsqrtf(run_var[c] + eps);
+  scale_shift[c] = make_float2(sc, fmaf(-run_mean[c], sc, beta[c]));
+}
+
+// a = [relu](y*scale + shift [+ addend]); 8 channels per thread
+__global__ void bn_apply_kernel(const BF8* __restrict__ y, const float2* __restrict__ scale_shift,
+                                const BF8* __restrict__ addend, BF8* __restrict__ out,
+                                long long n_vec, int c8, int relu) {
+  extern __shared__ float2 s_ss[];
+  for (int i = threadIdx.x; i < c8 * 8; i += blockDim.x) s_ss[i] = scale_shift[i];
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) {
+    const int cg = (int)(i % c8);
+    float f[8];
+    unpack8(y[i], f);
+    float ad[8];
+    if (addend != nullptr) unpack8(addend[i], ad);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float2 ss = s_ss[cg * 8 + k];
+      float v = fmaf(f[k], ss.x, ss.y);
+      if (addend != nullptr) v += ad[k];
+      f[k] = relu ? fmaxf(v, 0.f) : v;
+    }
+    out[i] = pack8(f);
+  }
+}
+
+// per-channel sum and sum of squares of a [M][C] tensor (standalone producer of BN statistics)
+__global__ void bn_stats_kernel(const BF8* __restrict__ y, float* __restrict__ stats, int stats_ld,
+                                long long M, int c8) {
+  __shared__ float s_acc[kThreads * 16];
+  const int cg = threadIdx.x % c8;
+  const int pl = threadIdx.x / c8;
+  const int lanes = kThreads / c8;
+  float s1[8], s2[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+  for (long long m = (long long)blockIdx.x * lanes + pl; m < M; m += (long long)gridDim.x * lanes) {
+    float f[8];
+    unpack8(y[m * c8 + cg], f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      s1[k] += f[k];
+      s2[k] = fmaf(f[k], f[k], s2[k]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    s_acc[threadIdx.x * 16 + k] = s1[k];
+    s_acc[threadIdx.x * 16 + 8 + k] = s2[k];
+  }
+  __syncthreads();
+  // thread t < c8*16 reduces one (channel, which) pair over the pixel lanes
+  for (int t = threadIdx.x; t < c8 * 16; t += blockDim.x) {
+    const int g = t / 16, k = t % 16;
+    float a = 0.f;
+    for (int l = 0; l < lanes; ++l) a += s_acc[(l * c8 + g) * 16 + k];
+    const int ch = g * 8 + (k & 7);
+    atomicAdd(stats + (k >> 3) * stats_ld + ch, a);
+  }
+}
+
+// dm = (da [+ addend]) * [y*scale+shift > 0];  stats += (sum dm, sum dm*y).
+// addend may be a stride-2 "compact" tensor [N, H/2.., W/2.., C] that is added at even pixels
+// (the gradient of a 1x1/stride-2 projection shortcut), or a per-image vector [N][C] scaled by
+// `bcast_scale` (the gradient of the global average pool).
+__global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8* __restrict__ addend,
+                                          int addend_kind, int H, int W, int Ha, int Wa,
+                                          float bcast_scale, const BF8* __restrict__ y,
+                                          const float2* __restrict__ scale_shift,
+                                          BF8* __restrict__ dm, float* __restrict__ stats,
+                                          int stats_ld, long long M, int c8) {
+  __shared__ float s_acc[kThreads * 16];
+  const int cg = threadIdx.x % c8;
+  const int pl = threadIdx.x / c8;
+  const int lanes = kThreads / c8;
+  float2 ss[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) ss[k] = scale_shift[cg * 8 + k];
+  float s1[8], s2[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+  for (long long m = (long long)blockIdx.x * lanes + pl; m < M; m += (long long)gridDim.x * lanes) {
+    float g[8], yy[8];
+    if (da != nullptr) {
+      unpack8(da[m * c8 + cg], g);
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = 0.f;
+    }
+    unpack8(y[m * c8 + cg], yy);
+    if (addend_kind == 1) {  // same shape
+      float a[8];
+      unpack8(addend[m * c8 + cg], a);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += a[k];
+    } else if (addend_kind == 2) {  // compact stride-2 tensor
+      const int w = (int)(m % W);
+      const long long t = m / W;
+      const int h = (int)(t % H);
+      const long long n = t / H;
+      if (((h | w) & 1) == 0 && (h >> 1) < Ha && (w >> 1) < Wa) {
+        float a[8];
+        unpack8(addend[((n * Ha + (h >> 1)) * Wa + (w >> 1)) * c8 + cg], a);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] += a[k];
+      }
+    } else if (addend_kind == 3) {  // per-image broadcast
+      const long long n = m / ((long long)H * W);
+      float a[8];
+      unpack8(addend[n * c8 + cg], a);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = fmaf(a[k], bcast_scale, g[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      g[k] = fmaf(yy[k], ss[k].x, ss[k].y) > 0.f ? g[k] : 0.f;
+    }
+    const BF8 packed = pack8(g);
+    dm[m * c8 + cg] = packed;
+    float gq[8];
+    unpack8(packed, gq);  // reduce what was stored (bf16-rounded), like the fused epilogue does
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      s1[k] += gq[k];
+      s2[k] = fmaf(gq[k], yy[k], s2[k]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    s_acc[threadIdx.x * 16 + k] = s1[k];
+    s_acc[threadIdx.x * 16 + 8 + k] = s2[k];
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < c8 * 16; t += blockDim.x) {
+    const int g = t / 16, k = t % 16;
+    float a = 0.f;
+    for (int l = 0; l < lanes; ++l) a += s_acc[(l * c8 + g) * 16 + k];
+    atomicAdd(stats + (k >> 3) * stats_ld + g * 8 + (k & 7), a);
+  }
+}
+
+// dgamma, dbeta and the coefficients of dy = A*dm + B*y + C
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ stats, int stats_ld,
+                                       float inv_count, const float* __restrict__ gamma,
+                                       const float2* __restrict__ mean_invstd,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                       float4* __restrict__ coef, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float s1 = stats[c], s2 = stats[stats_ld + c];
+  const float2 mi = mean_invstd[c];
+  const float dg = mi.y * (s2 - mi.x * s1);  // sum dm * xhat
+  if (dgamma != nullptr) {
+    dgamma[c] += dg;
+    dbeta[c] += s1;
+  }
+  const float a = gamma[c] * mi.y;
+  const float b = -a * mi.y * dg * inv_count;
+  const float cc = -a * s1 * inv_count - b * mi.x;
+  coef[c] = make_float4(a, b, cc, 0.f);
+}
+
+__global__ void bn_bwd_apply_kernel(const BF8* __restrict__ dm, const BF8* __restrict__ y,
+                                    const float4* __restrict__ coef, const BF8* __restrict__ addend,
+                                    BF8* __restrict__ dy, long long n_vec, int c8) {
+  extern __shared__ float4 s_coef[];
+  for (int i = threadIdx.x; i < c8 * 8; i += blockDim.x) s_coef[i] = coef[i];
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) {
+    const int cg = (int)(i % c8);
+    float g[8], yy[8], ad[8];
+    unpack8(dm[i], g);
+    unpack8(y[i], yy);
+    if (addend != nullptr) unpack8(addend[i], ad);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float4 cf = s_coef[cg * 8 + k];
+      float v = fmaf(cf.x, g[k], fmaf(cf.y, yy[k], cf.z));
+      if (addend != nullptr) v += ad[k];
+      g[k] = v;
+    }
+    dy[i] = pack8(g);
+  }
+}
+
+int check_c(int C, const char* who) {
+  const int c8 = C / 8;
+  if (C % 8 != 0 || c8 > kThreads || (c8 & (c8 - 1)) != 0)
+    return fail("%s: C=%d must be 8 * a power of two <= 2048", who, C);
+  return 0;
+}
+
+int ew_grid(long long n_vec) {
+  long long blocks = (n_vec + kThreads - 1) / kThreads;
+  const long long cap = (long long)num_sms() * 8;
+  return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+}  // namespace
+}  // namespace drn
+
+using namespace drn;
+
+extern "C" int drn_bn_finalize(const float* stats, int stats_ld, long long count, const float* gamma,
+                               const float* beta, float* run_mean, float* run_var, float decay,
+                               float eps, void* scale_shift, void* mean_invstd, int C,
+                               void* stream) {
+  DRN_REQUIRE(count > 0, "bn_finalize: count must be positive");
+  const float unbias = count > 1 ? (float)((double)count / (double)(count - 1)) : 1.f;
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      stats, stats_ld, (float)(1.0 / (double)count), unbias, gamma, beta, run_mean, run_var,
+      1.f - decay, eps, (float2*)scale_shift, (float2*)mean_invstd, C);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_bn_inference_params(const float* gamma, const float* beta, const float* run_mean,
+                                       const float* run_var, float eps, void* scale_shift, int C,
+                                       void* stream) {
+  bn_inference_params_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      gamma, beta, run_mean, run_var, eps, (float2*)scale_shift, C);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_bn_apply(const void* y, const void* scale_shift, const void* addend, void* out,
+                            long long M, int C, int relu, void* stream) {
+  DRN_REQUIRE(C % 8 == 0 && C <= 4096, "bn_apply: C=%d must be a multiple of 8, <= 4096", C);
+  const long long n_vec = M * (C / 8);
+  bn_apply_kernel<<<ew_grid(n_vec), kThreads, C * sizeof(float2), (cudaStream_t)stream>>>(
+      (const BF8*)y, (const float2*)scale_shift, (const BF8*)addend, (BF8*)out, n_vec, C / 8, relu);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_bn_stats(const void* y, float* stats, int stats_ld, long long M, int C,
+                            void* stream) {
+  if (int e = check_c(C, "bn_stats")) return e;
+  const int lanes = kThreads / (C / 8);
+  long long blocks = (M + lanes - 1) / lanes;
+  const long long cap = (long long)num_sms() * 4;
+  if (blocks > cap) blocks = cap;
+  bn_stats_kernel<<<(int)blocks, kThreads, 0, (cudaStream_t)stream>>>((const BF8*)y, stats,
+                                                                      stats_ld, M, C / 8);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int addend_kind, int N,
+                                      int H, int W, int Ha, int Wa, float bcast_scale,
+                                      const void* y, const void* scale_shift, void* dm, float* stats,
+                                      int stats_ld, int C, void* stream) {
+  if (int e = check_c(C, "bn_bwd_mask_reduce")) return e;
+  DRN_REQUIRE(addend_kind >= 0 && addend_kind <= 3, "bn_bwd_mask_reduce: bad addend_kind");
+  DRN_REQUIRE(addend_kind == 0 || addend != nullptr, "bn_bwd_mask_reduce: addend missing");
+  DRN_REQUIRE(da != nullptr || addend_kind != 0, "bn_bwd_mask_reduce: no gradient given");
+  const long long M = (long long)N * H * W;
+  const int lanes = kThreads / (C / 8);
+  long long blocks = (M + lanes - 1) / lanes;
+  const long long cap = (long long)num_sms() * 4;
+  if (blocks > cap) blocks = cap;
+  bn_bwd_mask_reduce_kernel<<<(int)blocks, kThreads, 0, (cudaStream_t)stream>>>(
+      (const BF8*)da, (const BF8*)addend, addend_kind, H, W, Ha, Wa, bcast_scale, (const BF8*)y,
+      (const float2*)scale_shift, (BF8*)dm, stats, stats_ld, M, C / 8);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_bn_bwd_finalize(const float* stats, int stats_ld, long long count,
+                                   const float* gamma, const void* mean_invstd, float* dgamma,
+                                   float* dbeta, void* coef, int C, void* stream) {
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      stats, stats_ld, (float)(1.0 / (double)count), gamma, (const float2*)mean_invstd, dgamma,
+      dbeta, (float4*)coef, C);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_bn_bwd_apply(const void* dm, const void* y, const void* coef, const void* addend,
+                                void* dy, long long M, int C, void* stream) {
+  DRN_REQUIRE(C % 8 == 0 && C <= 2048, "bn_bwd_apply: C=%d must be a multiple of 8, <= 2048", C);
+  const long long n_vec = M * (C / 8);
+  bn_bwd_apply_kernel<<<ew_grid(n_vec), kThreads, C * sizeof(float4), (cudaStream_t)stream>>>(
+      (const BF8*)dm, (const BF8*)y, (const float4*)coef, (const BF8*)addend, (BF8*)dy, n_vec,
+      C / 8);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

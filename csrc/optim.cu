@@ -1,0 +1,167 @@
+// Optimizer and weight-layout kernels.
+//
+// drn_sgd_momentum: the reference's update (resnet_model.py:85-99): L2 weight decay on EVERY
+//   trainable tensor (BN gamma/beta and the dense bias included), then
+//   m = mu*m + g ; w = w - lr*m   (tf.train.MomentumOptimizer, no Nesterov), on fp32 master
+//   weights kept in one flat arena; also writes the bf16 working copy the convolutions read,
+//   clears the gradient (wgrad accumulates with atomics) and returns sum(w^2) for the reported
+//   cost.  Hyper-parameters live in device memory so a captured CUDA graph follows the schedule.
+//   Ops K17, K19.
+// drn_weight_prep_dgrad: builds the flipped + transposed bf16 filter bank that turns the
+//   implicit-GEMM forward kernel into the data-gradient kernel.
+// drn_upsample_zero: zero-insertion of dy for the data gradient of strided convolutions.
+#include "common.cuh"
+#include "host.cuh"
+#include "../include/drn_b200.h"
+
+namespace drn {
+namespace {
+
+__global__ void sgd_momentum_kernel(float4* __restrict__ w, float4* __restrict__ g,
+                                    float4* __restrict__ m, uint2* __restrict__ shadow,
+                                    long long n4, const float* __restrict__ hyper,
+                                    float* __restrict__ l2_sum, int zero_grad) {
+  const float lr = hyper[0], mu = hyper[1], wd = hyper[2], gs = hyper[3];
+  float l2 = 0.f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 wv = w[i], gv = g[i], mv = m[i];
+    l2 += wv.x * wv.x + wv.y * wv.y + wv.z * wv.z + wv.w * wv.w;
+    mv.x = fmaf(mu, mv.x, fmaf(wd, wv.x, gv.x * gs));
+    mv.y = fmaf(mu, mv.y, fmaf(wd, wv.y, gv.y * gs));
+    mv.z = fmaf(mu, mv.z, fmaf(wd, wv.z, gv.z * gs));
+    mv.w = fmaf(mu, mv.w, fmaf(wd, wv.w, gv.w * gs));
+    wv.x = fmaf(-lr, mv.x, wv.x);
+    wv.y = fmaf(-lr, mv.y, wv.y);
+    wv.z = fmaf(-lr, mv.z, wv.z);
+    wv.w = fmaf(-lr, mv.w, wv.w);
+    w[i] = wv;
+    m[i] = mv;
+    if (zero_grad) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (shadow) shadow[i] = make_uint2(pack_bf16x2(wv.x, wv.y), pack_bf16x2(wv.z, wv.w));
+  }
+  if (l2_sum != nullptr) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) l2 += __shfl_xor_sync(0xffffffffu, l2, o);
+    __shared__ float s[32];
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = l2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += s[i];
+      atomicAdd(l2_sum, t);
+    }
+  }
+}
+
+// dst[c][R-1-r][S-1-s][k] = src[k][r][s][c]     (32x32 smem tile transpose per filter tap)
+__global__ void weight_prep_dgrad_kernel(const __nv_bfloat16* __restrict__ src,
+                                         __nv_bfloat16* __restrict__ dst, int K, int RS, int C) {
+  __shared__ __nv_bfloat16 tile[32][33];
+  const int tap = blockIdx.z;
+  const int c0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int k = k0 + j, c = c0 + threadIdx.x;
+    if (k < K && c < C) tile[j][threadIdx.x] = src[((long long)k * RS + tap) * C + c];
+  }
+  __syncthreads();
+  const int ftap = RS - 1 - tap;  // flipping r and s together reverses the linear tap index
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int c = c0 + j, k = k0 + threadIdx.x;
+    if (k < K && c < C) dst[((long long)c * RS + ftap) * K + k] = tile[threadIdx.x][j];
+  }
+}
+
+// out[n, p*s, q*s, :] = dy[n, p, q, :], zeros elsewhere. 8 channels per thread.
+__global__ void upsample_zero_kernel(const uint4* __restrict__ dy, uint4* __restrict__ out, int N,
+                                     int P, int Q, int U, int V, int c8, int stride) {
+  const long long total = (long long)N * U * V * c8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c8);
+    long long t = i / c8;
+    const int v = (int)(t % V);
+    t /= V;
+    const int u = (int)(t % U);
+    const long long n = t / U;
+    uint4 val = make_uint4(0, 0, 0, 0);
+    if (u % stride == 0 && v % stride == 0) {
+      const int p = u / stride, q = v / stride;
+      if (p < P && q < Q) val = dy[((n * P + p) * Q + q) * c8 + cg];
+    }
+    out[i] = val;
+  }
+}
+
+__global__ void f32_to_bf16_kernel(const float4* __restrict__ src, uint2* __restrict__ dst,
+                                   long long n4) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = src[i];
+    dst[i] = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+  }
+}
+
+__global__ void mul_inplace_kernel(float* __restrict__ a, const float* __restrict__ b, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    a[i] *= b[i];
+}
+
+int ew_grid(long long n, int threads) {
+  long long blocks = (n + threads - 1) / threads;
+  const long long cap = (long long)num_sms() * 8;
+  return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+}  // namespace
+}  // namespace drn
+
+using namespace drn;
+
+// n must be a multiple of 4 (pad the arena). hyper = device float[4] {lr, momentum, wd, grad_scale}.
+extern "C" int drn_sgd_momentum(float* master, float* grad, float* mom, void* shadow_bf16,
+                                long long n, const float* hyper, float* l2_sum, int zero_grad,
+                                void* stream) {
+  DRN_REQUIRE(n % 4 == 0, "sgd_momentum: n must be a multiple of 4");
+  const long long n4 = n / 4;
+  sgd_momentum_kernel<<<ew_grid(n4, 256), 256, 0, (cudaStream_t)stream>>>(
+      (float4*)master, (float4*)grad, (float4*)mom, (uint2*)shadow_bf16, n4, hyper, l2_sum,
+      zero_grad);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_weight_prep_dgrad(const void* w_krsc, void* w_dgrad, int K, int R, int S, int C,
+                                     void* stream) {
+  dim3 grid((C + 31) / 32, (K + 31) / 32, R * S), block(32, 8);
+  weight_prep_dgrad_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)w_krsc, (__nv_bfloat16*)w_dgrad, K, R * S, C);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_upsample_zero(const void* dy, void* out, int N, int P, int Q, int U, int V, int C,
+                                 int stride, void* stream) {
+  DRN_REQUIRE(C % 8 == 0, "upsample_zero: C must be a multiple of 8");
+  const long long total = (long long)N * U * V * (C / 8);
+  upsample_zero_kernel<<<ew_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)dy, (uint4*)out, N, P, Q, U, V, C / 8, stride);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
+  DRN_REQUIRE(n % 4 == 0, "f32_to_bf16: n must be a multiple of 4");
+  f32_to_bf16_kernel<<<ew_grid(n / 4, 256), 256, 0, (cudaStream_t)stream>>>((const float4*)src,
+                                                                            (uint2*)dst, n / 4);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// a[i] *= b[i]  (used to keep the structurally-zero taps of the space-to-depth stem filter at zero)
+extern "C" int drn_mul_inplace_f32(float* a, const float* b, long long n, void* stream) {
+  mul_inplace_kernel<<<ew_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(a, b, n);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

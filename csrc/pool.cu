@@ -1,0 +1,198 @@
+// Pooling kernels (NHWC bf16, 8 channels per thread).
+//   - 3x3/stride-2 max pool with TF "SAME" padding (reference resnet_model_official.py:314-316;
+//     112 -> 56 pads 0 before / 1 after) + its backward through a stored arg-max   (op K11)
+//   - global average pool fused with the final BatchNorm+ReLU (resnet_model_official.py:266-271,
+//     334-339)                                                                     (ops K8/K9/K12)
+//     (its backward is drn_bn_bwd_mask_reduce with addend_kind = 3).
+#include "common.cuh"
+#include "host.cuh"
+#include "../include/drn_b200.h"
+
+namespace drn {
+namespace {
+
+struct alignas(16) BF8 {
+  uint32_t v[4];
+};
+struct alignas(8) U8x8 {
+  uint8_t v[8];
+};
+
+__device__ __forceinline__ void unpack8(const BF8& p, float (&f)[8]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = bf16lo(p.v[i]);
+    f[2 * i + 1] = bf16hi(p.v[i]);
+  }
+}
+__device__ __forceinline__ BF8 pack8(const float (&f)[8]) {
+  BF8 p;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) p.v[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
+  return p;
+}
+
+__global__ void maxpool_fwd_kernel(const BF8* __restrict__ x, BF8* __restrict__ out,
+                                   U8x8* __restrict__ argmax, int N, int H, int W, int c8, int P,
+                                   int Q, int ksize, int stride, int pad_lo) {
+  const long long total = (long long)N * P * Q * c8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c8);
+    long long t = i / c8;
+    const int q = (int)(t % Q);
+    t /= Q;
+    const int p = (int)(t % P);
+    const long long n = t / P;
+    float best[8];
+    uint8_t arg[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      best[k] = -INFINITY;
+      arg[k] = 0xff;
+    }
+    for (int r = 0; r < ksize; ++r) {
+      const int h = p * stride - pad_lo + r;
+      if (h < 0 || h >= H) continue;
+      for (int s = 0; s < ksize; ++s) {
+        const int w = q * stride - pad_lo + s;
+        if (w < 0 || w >= W) continue;
+        float f[8];
+        unpack8(x[((n * H + h) * W + w) * c8 + cg], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (f[k] > best[k]) {  // strict: first maximum wins, like cuDNN/TF
+            best[k] = f[k];
+            arg[k] = (uint8_t)(r * ksize + s);
+          }
+        }
+      }
+    }
+    out[i] = pack8(best);
+    U8x8 a;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a.v[k] = arg[k];
+    argmax[i] = a;
+  }
+}
+
+// gather formulation: each input pixel sums the gradients of the windows that chose it
+__global__ void maxpool_bwd_kernel(const BF8* __restrict__ dy, const U8x8* __restrict__ argmax,
+                                   BF8* __restrict__ dx, int N, int H, int W, int c8, int P, int Q,
+                                   int ksize, int stride, int pad_lo) {
+  const long long total = (long long)N * H * W * c8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c8);
+    long long t = i / c8;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const long long n = t / H;
+    float g[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = 0.f;
+    for (int r = 0; r < ksize; ++r) {
+      const int hp = h + pad_lo - r;
+      if (hp < 0 || hp % stride != 0) continue;
+      const int p = hp / stride;
+      if (p >= P) continue;
+      for (int s = 0; s < ksize; ++s) {
+        const int wq = w + pad_lo - s;
+        if (wq < 0 || wq % stride != 0) continue;
+        const int q = wq / stride;
+        if (q >= Q) continue;
+        const long long o = ((n * P + p) * Q + q) * c8 + cg;
+        const U8x8 a = argmax[o];
+        float d[8];
+        unpack8(dy[o], d);
+        const uint8_t me = (uint8_t)(r * ksize + s);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (a.v[k] == me) g[k] += d[k];
+      }
+    }
+    dx[i] = pack8(g);
+  }
+}
+
+// out[n][c] = mean_{hw} relu(y*scale + shift)      (one block per image)
+__global__ void bnrelu_avgpool_kernel(const BF8* __restrict__ y,
+                                      const float2* __restrict__ scale_shift, BF8* __restrict__ out,
+                                      int HW, int c8, float inv_hw) {
+  __shared__ float s_acc[256 * 8];
+  const int n = blockIdx.x;
+  const int cg = threadIdx.x % c8;
+  const int pl = threadIdx.x / c8;
+  const int lanes = blockDim.x / c8;
+  float2 ss[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) ss[k] = scale_shift[cg * 8 + k];
+  float acc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+  for (int px = pl; px < HW; px += lanes) {
+    float f[8];
+    unpack8(y[((long long)n * HW + px) * c8 + cg], f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] += fmaxf(fmaf(f[k], ss[k].x, ss[k].y), 0.f);
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s_acc[threadIdx.x * 8 + k] = acc[k];
+  __syncthreads();
+  if (pl == 0) {
+    float r[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r[k] = 0.f;
+    for (int l = 0; l < lanes; ++l)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) r[k] += s_acc[(l * c8 + cg) * 8 + k];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r[k] *= inv_hw;
+    out[(long long)n * c8 + cg] = pack8(r);
+  }
+}
+
+}  // namespace
+}  // namespace drn
+
+using namespace drn;
+
+static int grid_for(long long total) {
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)num_sms() * 8;
+  return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+extern "C" int drn_maxpool_fwd(const void* x, void* out, void* argmax, int N, int H, int W, int C,
+                               int ksize, int stride, int pad_lo, int P, int Q, void* stream) {
+  DRN_REQUIRE(C % 8 == 0, "maxpool: C must be a multiple of 8");
+  DRN_REQUIRE(ksize * ksize < 255, "maxpool: window too large");
+  const long long total = (long long)N * P * Q * (C / 8);
+  maxpool_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+      (const BF8*)x, (BF8*)out, (U8x8*)argmax, N, H, W, C / 8, P, Q, ksize, stride, pad_lo);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_maxpool_bwd(const void* dy, const void* argmax, void* dx, int N, int H, int W,
+                               int C, int ksize, int stride, int pad_lo, int P, int Q,
+                               void* stream) {
+  DRN_REQUIRE(C % 8 == 0, "maxpool: C must be a multiple of 8");
+  const long long total = (long long)N * H * W * (C / 8);
+  maxpool_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+      (const BF8*)dy, (const U8x8*)argmax, (BF8*)dx, N, H, W, C / 8, P, Q, ksize, stride, pad_lo);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int drn_bnrelu_avgpool(const void* y, const void* scale_shift, void* out, int N, int HW,
+                                  int C, void* stream) {
+  const int c8 = C / 8;
+  DRN_REQUIRE(C % 8 == 0 && c8 <= 256 && (c8 & (c8 - 1)) == 0,
+              "bnrelu_avgpool: C=%d must be 8 * a power of two <= 2048", C);
+  bnrelu_avgpool_kernel<<<N, 256, 0, (cudaStream_t)stream>>>(
+      (const BF8*)y, (const float2*)scale_shift, (BF8*)out, HW, c8, 1.f / (float)HW);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

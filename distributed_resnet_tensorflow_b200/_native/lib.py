@@ -39,6 +39,25 @@ _SIGNATURES = {
     "drn_num_sms": (_i, []),
     "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
+    "drn_bn_finalize": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _i, _vp]),
+    "drn_bn_inference_params": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _i, _vp]),
+    "drn_bn_apply": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp]),
+    "drn_bn_stats": (_i, [_vp, _vp, _i, _ll, _i, _vp]),
+    "drn_bn_bwd_mask_reduce": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "drn_bn_bwd_finalize": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "drn_bn_bwd_apply": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _i, _vp]),
+    "drn_maxpool_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "drn_maxpool_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "drn_bnrelu_avgpool": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "drn_softmax_xent": (_i, [_vp, _i, _vp, _vp, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "drn_sgd_momentum": (_i, [_vp, _vp, _vp, _vp, _ll, _vp, _vp, _i, _vp]),
+    "drn_weight_prep_dgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "drn_upsample_zero": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "drn_f32_to_bf16": (_i, [_vp, _vp, _ll, _vp]),
+    "drn_mul_inplace_f32": (_i, [_vp, _vp, _ll, _vp]),
+    "drn_cifar_augment": (_i, [_vp, _i, _i, _vp, _i, _i, _i, ctypes.c_ulonglong, ctypes.c_uint, _ll, _i, _vp]),
+    "drn_imagenet_prep": (_i, [_vp, _ll, _i, _i, _vp, _vp, _i, _i, _f, _f, _f, _vp]),
+    "drn_resize_bilinear": (_i, [_vp, _i, _i, _vp, _i, _i, _vp]),
 }
 
 

@@ -1,0 +1,640 @@
+"""Native sm_100a executor of a pre-activation ``NetSpec``: static buffers, one flat parameter
+arena, and a fixed schedule of hand-written kernels (csrc/*.cu) that is captured in a CUDA graph.
+
+Data flow of one v2 block (reference resnet_model_official.py:94-175), forward:
+
+    x (raw residual stream, bf16 NHWC)  --stats from producer epilogue-->  bn_finalize
+    a0 = bn_apply(x)                               shortcut = x  or  conv1x1(a0)  [projection]
+    y1 = conv(a0) [+stats] -> a1 = bn_apply(y1) -> y2 = conv(a1) [+stats] -> a2 -> ...
+    out = conv(a_last) + shortcut [+stats for the next block]        (residual add in the epilogue)
+
+backward: every dgrad is the same implicit-GEMM kernel on flipped filters; its epilogue applies
+the ReLU/BN mask and accumulates the two BN-backward reductions, ``bn_bwd_apply`` turns the masked
+gradient into the gradient of the raw tensor (adding the identity-shortcut gradient on the way),
+wgrads accumulate straight into the fp32 gradient arena that the optimizer / collectives consume.
+
+Gradient averaging across replicas, the optimizer step and the PS-style sharded update live in
+``parallel/``; this class only exposes the arenas (``master``, ``grad``, ``mom``, ``shadow``).
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from .._native import lib as _nl
+from .._native.lib import ConvDesc, EPI_BNBWD, EPI_PLAIN, EPI_RESADD
+from ..ops.conv import ConvGeom
+from .spec import BlockSpec, BNSpec, ConvSpec, NetSpec
+
+BN_DECAY = 0.997
+BN_EPS = 1e-5
+VGG_MEANS = (123.68 / 255.0, 116.78 / 255.0, 103.94 / 255.0)  # vgg_preprocessing.py:37-39 (in [0,1] units)
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def padded_classes(n: int) -> int:
+    if n <= 16:
+        return 16
+    if n <= 32:
+        return 32
+    if n <= 256:
+        return _round_up(n, 64)
+    return _round_up(n, 256)
+
+
+# ------------------------------------------------------------------------------------------------
+# parameter arena layout
+# ------------------------------------------------------------------------------------------------
+@dataclass
+class ParamEntry:
+    name: str
+    tf_shape: Tuple[int, ...]
+    dev_shape: Tuple[int, ...]
+    offset: int
+    kind: str  # conv | stem_cifar | stem_s2d | dense_kernel | vector
+
+    @property
+    def numel(self) -> int:
+        return int(np.prod(self.dev_shape))
+
+
+def _s2d_index_maps():
+    """For the 7x7/2 ImageNet stem rewritten as a 4x4/1 convolution over the space-to-depth input:
+    (r, s, c) of the 7x7x3 filter -> (a_y, a_x, ch16) of the 4x4x16 filter."""
+    idx = []
+    for r in range(7):
+        ay, by = divmod(r + 1, 2)
+        for s in range(7):
+            ax, bx = divmod(s + 1, 2)
+            for c in range(3):
+                idx.append((r, s, c, ay, ax, (by * 2 + bx) * 3 + c))
+    return idx
+
+
+class ParamLayout:
+    ALIGN = 64
+
+    def __init__(self, spec: NetSpec):
+        self.spec = spec
+        self.entries: Dict[str, ParamEntry] = {}
+        self.order: List[str] = []
+        off = 0
+        stem_name = f"{spec.stem.name}/kernel"
+        for name, shp in spec.trainable_variables():
+            if name == stem_name:
+                if spec.dataset == "imagenet":
+                    kind, dshape = "stem_s2d", (shp[3], 4, 4, 16)
+                else:
+                    kind, dshape = "stem_cifar", (shp[3], shp[0], shp[1], 16)
+            elif name.endswith("/kernel") and len(shp) == 4:
+                kind, dshape = "conv", (shp[3], shp[0], shp[1], shp[2])
+            elif name == "dense/kernel":
+                kind, dshape = "dense_kernel", (padded_classes(shp[1]), shp[0])
+            else:
+                kind, dshape = "vector", tuple(shp)
+            e = ParamEntry(name, tuple(shp), dshape, off, kind)
+            self.entries[name] = e
+            self.order.append(name)
+            off = _round_up(off + e.numel, self.ALIGN)
+        self.total = _round_up(off, 1024)
+
+    def to_dev(self, name: str, arr: np.ndarray) -> np.ndarray:
+        e = self.entries[name]
+        arr = np.asarray(arr, np.float32)
+        assert tuple(arr.shape) == e.tf_shape, (name, arr.shape, e.tf_shape)
+        if e.kind == "conv":
+            return np.ascontiguousarray(arr.transpose(3, 0, 1, 2))
+        if e.kind == "stem_cifar":
+            out = np.zeros(e.dev_shape, np.float32)
+            out[:, :, :, :3] = arr.transpose(3, 0, 1, 2)
+            return out
+        if e.kind == "stem_s2d":
+            out = np.zeros(e.dev_shape, np.float32)
+            for r, s, c, ay, ax, ch in _s2d_index_maps():
+                out[:, ay, ax, ch] = arr[r, s, c, :]
+            return out
+        if e.kind == "dense_kernel":
+            out = np.zeros(e.dev_shape, np.float32)
+            out[: arr.shape[1], :] = arr.T
+            return out
+        return arr
+
+    def to_tf(self, name: str, dev: np.ndarray) -> np.ndarray:
+        e = self.entries[name]
+        dev = np.asarray(dev, np.float32).reshape(e.dev_shape)
+        if e.kind == "conv":
+            return np.ascontiguousarray(dev.transpose(1, 2, 3, 0))
+        if e.kind == "stem_cifar":
+            return np.ascontiguousarray(dev[:, :, :, :3].transpose(1, 2, 3, 0))
+        if e.kind == "stem_s2d":
+            out = np.zeros(e.tf_shape, np.float32)
+            for r, s, c, ay, ax, ch in _s2d_index_maps():
+                out[r, s, c, :] = dev[:, ay, ax, ch]
+            return out
+        if e.kind == "dense_kernel":
+            return np.ascontiguousarray(dev[: e.tf_shape[1], :].T)
+        return dev.copy()
+
+    def stem_mask(self) -> Optional[np.ndarray]:
+        """1 where the s2d stem filter has a real tap, 0 at structural zeros."""
+        e = self.entries[f"{self.spec.stem.name}/kernel"]
+        if e.kind != "stem_s2d":
+            return None
+        m = np.zeros(e.dev_shape, np.float32)
+        for r, s, c, ay, ax, ch in _s2d_index_maps():
+            m[:, ay, ax, ch] = 1.0
+        return m
+
+
+# ------------------------------------------------------------------------------------------------
+# engine
+# ------------------------------------------------------------------------------------------------
+def _p(t) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+class _BN:
+    """Per-BatchNorm device state."""
+
+    def __init__(self, spec: BNSpec, eng: "NativeResNet"):
+        self.spec = spec
+        C = spec.channels
+        self.C = C
+        self.gamma = eng.param_view(f"{spec.name}/gamma")
+        self.beta = eng.param_view(f"{spec.name}/beta")
+        self.dgamma = eng.grad_view(f"{spec.name}/gamma")
+        self.dbeta = eng.grad_view(f"{spec.name}/beta")
+        self.run_mean = torch.zeros(C, device=eng.device)
+        self.run_var = torch.ones(C, device=eng.device)
+        self.fstats = eng.alloc_stats(C)
+        self.bstats = eng.alloc_stats(C)
+        self.ss = torch.zeros((C, 2), device=eng.device)
+        self.mi = torch.zeros((C, 2), device=eng.device)
+        self.coef = torch.zeros((C, 4), device=eng.device)
+
+
+class _Conv:
+    def __init__(self, spec: ConvSpec, eng: "NativeResNet", geom: ConvGeom, need_dgrad: bool):
+        self.spec = spec
+        self.g = geom
+        self.desc = geom.desc()
+        name = f"{spec.name}/kernel"
+        self.w = eng.shadow_view(name)
+        self.dw = eng.grad_view(name)
+        self.wd = None
+        self.dg = None
+        self.up = None
+        if need_dgrad:
+            self.wd = torch.zeros(geom.K * geom.R * geom.S * geom.C, dtype=torch.bfloat16,
+                                  device=eng.device)
+            self.dg = geom.dgrad_geom()
+            self.dg_desc = self.dg.desc()
+            if geom.stride > 1 and geom.R > 1:
+                self.up = torch.zeros((geom.N, self.dg.H, self.dg.W, geom.K), dtype=torch.bfloat16,
+                                      device=eng.device)
+
+
+class NativeResNet:
+    def __init__(self, spec: NetSpec, batch: int, device="cuda:0"):
+        if spec.version != 2:
+            raise NotImplementedError("the native engine implements the reference's v2 networks; "
+                                      "use --backend=torch for resnet_version=1")
+        _nl.load()
+        self.spec = spec
+        self.B = batch
+        self.device = torch.device(device)
+        self.layout = ParamLayout(spec)
+        n = self.layout.total
+        dev = self.device
+        self.master = torch.zeros(n, device=dev)
+        self.grad = torch.zeros(n, device=dev)
+        self.mom = torch.zeros(n, device=dev)
+        self.shadow = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+        self.hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0], device=dev)   # lr, momentum, wd, grad_scale
+        self.scalars = torch.zeros(4, device=dev)       # [0] loss_sum, [1] l2_sum
+        self.correct = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.global_step = 0
+        self._stats_chunks: List[torch.Tensor] = []
+        self._stats_arena = torch.zeros(2 * 2 * sum(b.channels for b in spec.bns()) * 2 + 4096, device=dev)
+        self._stats_off = 0
+        m = self.layout.stem_mask()
+        self.stem_mask = torch.from_numpy(m).to(dev).reshape(-1) if m is not None else None
+        self._build()
+
+    # ---- arena views ------------------------------------------------------------------------
+    def _view(self, arena, name):
+        e = self.layout.entries[name]
+        return arena[e.offset:e.offset + e.numel]
+
+    def param_view(self, name):
+        return self._view(self.master, name)
+
+    def grad_view(self, name):
+        return self._view(self.grad, name)
+
+    def shadow_view(self, name):
+        return self._view(self.shadow, name)
+
+    def alloc_stats(self, C: int) -> torch.Tensor:
+        off = self._stats_off
+        self._stats_off += 2 * C
+        assert self._stats_off <= self._stats_arena.numel()
+        return self._stats_arena[off:off + 2 * C].view(2, C)
+
+    def _act(self, n, h, w, c, dtype=torch.bfloat16):
+        return torch.empty((n, h, w, c), dtype=dtype, device=self.device)
+
+    # ---- plan ---------------------------------------------------------------------------------
+    def _geom(self, c: ConvSpec, cin_override: Optional[int] = None) -> ConvGeom:
+        lo, hi = c.pad
+        return ConvGeom(self.B, c.hin, c.hin, cin_override or c.cin, c.cout, c.ksize, c.ksize,
+                        c.stride, lo, hi)
+
+    def _build(self):
+        s, B = self.spec, self.B
+        # stem
+        if s.dataset == "imagenet":
+            self.in_h = s.image_size // 2
+            stem_geom = ConvGeom(B, self.in_h, self.in_h, 16, s.stem.cout, 4, 4, 1, 2, 1)
+        else:
+            self.in_h = s.image_size
+            stem_geom = self._geom(s.stem, cin_override=16)
+        self.x0 = self._act(B, self.in_h, self.in_h, 16)
+        self.labels = torch.zeros(B, dtype=torch.int32, device=self.device)
+        self.stem = _Conv(s.stem, self, stem_geom, need_dgrad=False)
+        self.y_stem = self._act(B, stem_geom.P, stem_geom.Q, s.stem.cout)
+        if s.maxpool:
+            hp = (stem_geom.P + 1) // 2
+            self.pool_out = self._act(B, hp, hp, s.stem.cout)
+            self.pool_arg = torch.empty((B, hp, hp, s.stem.cout), dtype=torch.uint8, device=self.device)
+        # blocks
+        self.blocks = []
+        for blk in s.blocks:
+            self.blocks.append(self._plan_block(blk))
+        self.final_bn = _BN(s.final_bn, self)
+        self.pooled = torch.empty((B, s.dense_in), dtype=torch.bfloat16, device=self.device)
+        kp = padded_classes(s.num_classes)
+        self.kp = kp
+        self.dense_geom = ConvGeom(B, 1, 1, s.dense_in, kp, 1, 1, 1, 0, 0)
+        self.dense_desc = self.dense_geom.desc()
+        self.dense_w = self.shadow_view("dense/kernel")
+        self.dense_dw = self.grad_view("dense/kernel")
+        self.dense_wd = torch.zeros(kp * s.dense_in, dtype=torch.bfloat16, device=self.device)
+        self.dense_dgeom = ConvGeom(B, 1, 1, kp, s.dense_in, 1, 1, 1, 0, 0)
+        self.dense_ddesc = self.dense_dgeom.desc()
+        self.dense_bias = self.param_view("dense/bias")
+        self.dense_dbias = self.grad_view("dense/bias")
+        self.logits = torch.empty((B, kp), dtype=torch.bfloat16, device=self.device)
+        self.dlogits = torch.empty((B, kp), dtype=torch.bfloat16, device=self.device)
+        self.d_pooled = torch.empty((B, s.dense_in), dtype=torch.bfloat16, device=self.device)
+        # backward scratch: a few buffers of the largest activation size
+        max_elems = max([self.y_stem.numel()] + [b["max_elems"] for b in self.blocks])
+        self._scratch = [torch.empty(max_elems, dtype=torch.bfloat16, device=self.device) for _ in range(6)]
+
+    def _plan_block(self, blk: BlockSpec) -> dict:
+        B = self.B
+        d = {"spec": blk}
+        d["bn0"] = _BN(blk.bns[0], self)
+        d["a0"] = self._act(B, blk.hin, blk.hin, blk.cin)
+        sizes = [d["a0"].numel()]
+        if blk.proj is not None:
+            d["proj"] = _Conv(blk.proj, self, self._geom(blk.proj), need_dgrad=True)
+            pg = d["proj"].g
+            d["proj_cdesc"] = ConvGeom(B, pg.P, pg.Q, pg.K, pg.C, 1, 1, 1, 0, 0).desc()
+            d["shortcut"] = self._act(B, blk.proj.hout, blk.proj.hout, blk.cout)
+            sizes.append(d["shortcut"].numel())
+        convs, bns, ys, acts = [], [], [], []
+        for i, c in enumerate(blk.convs):
+            convs.append(_Conv(c, self, self._geom(c), need_dgrad=True))
+            last = i + 1 == len(blk.convs)
+            y = self._act(B, c.hout, c.hout, c.cout)
+            ys.append(y)
+            sizes.append(y.numel())
+            if not last:
+                bns.append(_BN(blk.bns[i + 1], self))
+                acts.append(self._act(B, c.hout, c.hout, c.cout))
+        d.update(convs=convs, bns=bns, ys=ys, acts=acts, max_elems=max(sizes))
+        return d
+
+    # ---- variables in / out -----------------------------------------------------------------
+    def import_variables(self, variables: Dict[str, np.ndarray]) -> None:
+        host_w = np.zeros(self.layout.total, np.float32)
+        host_m = np.zeros(self.layout.total, np.float32)
+        for name in self.layout.order:
+            e = self.layout.entries[name]
+            host_w[e.offset:e.offset + e.numel] = self.layout.to_dev(name, variables[name]).reshape(-1)
+            slot = f"{name}/Momentum"
+            if slot in variables:
+                host_m[e.offset:e.offset + e.numel] = self.layout.to_dev(name, variables[slot]).reshape(-1)
+        self.master.copy_(torch.from_numpy(host_w))
+        self.mom.copy_(torch.from_numpy(host_m))
+        self.grad.zero_()
+        for bn in self._all_bns():
+            bn.run_mean.copy_(torch.from_numpy(np.asarray(variables[f"{bn.spec.name}/moving_mean"], np.float32)))
+            bn.run_var.copy_(torch.from_numpy(np.asarray(variables[f"{bn.spec.name}/moving_variance"], np.float32)))
+        self.global_step = int(variables.get("global_step", 0))
+        self.refresh_working_weights()
+
+    def export_variables(self, with_slots: bool = True) -> Dict[str, np.ndarray]:
+        torch.cuda.synchronize(self.device)
+        w = self.master.cpu().numpy()
+        m = self.mom.cpu().numpy()
+        out: Dict[str, np.ndarray] = {}
+        for name in self.layout.order:
+            e = self.layout.entries[name]
+            out[name] = self.layout.to_tf(name, w[e.offset:e.offset + e.numel])
+            if with_slots:
+                out[f"{name}/Momentum"] = self.layout.to_tf(name, m[e.offset:e.offset + e.numel])
+        for bn in self._all_bns():
+            out[f"{bn.spec.name}/moving_mean"] = bn.run_mean.cpu().numpy()
+            out[f"{bn.spec.name}/moving_variance"] = bn.run_var.cpu().numpy()
+        out["global_step"] = np.asarray(self.global_step, np.int64)
+        return out
+
+    def _all_bns(self) -> List[_BN]:
+        out = []
+        for b in self.blocks:
+            out.append(b["bn0"])
+            out.extend(b["bns"])
+        out.append(self.final_bn)
+        return out
+
+    def _all_convs(self) -> List[_Conv]:
+        out = [self.stem]
+        for b in self.blocks:
+            if "proj" in b:
+                out.append(b["proj"])
+            out.extend(b["convs"])
+        return out
+
+    # ---- kernels ------------------------------------------------------------------------------
+    @staticmethod
+    def _st() -> int:
+        return torch.cuda.current_stream().cuda_stream
+
+    def refresh_working_weights(self) -> None:
+        """bf16 working copy + flipped dgrad banks from the fp32 master (after import / update)."""
+        st = self._st()
+        _nl.call("drn_f32_to_bf16", _p(self.master), _p(self.shadow), self.layout.total, st)
+        self.prep_dgrad_weights()
+
+    def prep_dgrad_weights(self) -> None:
+        st = self._st()
+        for c in self._all_convs():
+            if c.wd is not None:
+                g = c.g
+                _nl.call("drn_weight_prep_dgrad", _p(c.w), _p(c.wd), g.K, g.R, g.S, g.C, st)
+        _nl.call("drn_weight_prep_dgrad", _p(self.dense_w), _p(self.dense_wd), self.kp, 1, 1,
+                 self.spec.dense_in, st)
+
+    def _conv(self, desc, x, w, y, side=None, stats=None, ss=None, mode=EPI_PLAIN):
+        _nl.call("drn_conv_igemm", ctypes.byref(desc), _p(x), _p(w), _p(y), _p(side), _p(stats),
+                 stats.stride(0) if stats is not None else 0, _p(ss), mode, 0, self._st())
+
+    def _wgrad(self, conv: _Conv, x, dy):
+        _nl.call("drn_conv_wgrad", ctypes.byref(conv.desc), _p(x), _p(dy), _p(conv.dw), 0, self._st())
+
+    def _bn_finalize(self, bn: _BN, count: int, training: bool):
+        st = self._st()
+        if training:
+            _nl.call("drn_bn_finalize", _p(bn.fstats), bn.fstats.stride(0), count, _p(bn.gamma),
+                     _p(bn.beta), _p(bn.run_mean), _p(bn.run_var), BN_DECAY, BN_EPS, _p(bn.ss),
+                     _p(bn.mi), bn.C, st)
+        else:
+            _nl.call("drn_bn_inference_params", _p(bn.gamma), _p(bn.beta), _p(bn.run_mean),
+                     _p(bn.run_var), BN_EPS, _p(bn.ss), bn.C, st)
+
+    def _bn_apply(self, bn: _BN, y, out):
+        M = y.numel() // bn.C
+        _nl.call("drn_bn_apply", _p(y), _p(bn.ss), 0, _p(out), M, bn.C, 1, self._st())
+
+    def _dgrad(self, conv: _Conv, dy, out, side=None, stats=None, ss=None, mode=EPI_PLAIN):
+        """Data gradient of ``conv`` given dy; writes [B, H, W, Cin] into ``out``."""
+        src = dy
+        if conv.g.stride > 1:
+            if conv.g.R == 1:
+                raise AssertionError("1x1 strided dgrad is handled by the caller (compact form)")
+            _nl.call("drn_upsample_zero", _p(dy), _p(conv.up), conv.g.N, conv.g.P, conv.g.Q,
+                     conv.dg.H, conv.dg.W, conv.g.K, conv.g.stride, self._st())
+            src = conv.up
+        self._conv(conv.dg_desc, src, conv.wd, out, side=side, stats=stats, ss=ss, mode=mode)
+
+    # ---- forward ------------------------------------------------------------------------------
+    def forward(self, training: bool = True) -> None:
+        """Consumes self.x0 / self.labels; produces self.logits (and saves what backward needs)."""
+        s = self.spec
+        st = self._st()
+        if training:
+            self._stats_arena.zero_()
+        first_bn = self.blocks[0]["bn0"]
+        if s.maxpool:
+            self._conv(self.stem.desc, self.x0, self.stem.w, self.y_stem)
+            g = self.stem.g
+            hp = self.pool_out.shape[1]
+            _nl.call("drn_maxpool_fwd", _p(self.y_stem), _p(self.pool_out), _p(self.pool_arg), self.B,
+                     g.P, g.Q, g.K, 3, 2, 0, hp, hp, st)
+            if training:
+                _nl.call("drn_bn_stats", _p(self.pool_out), _p(first_bn.fstats), first_bn.fstats.stride(0),
+                         self.pool_out.numel() // g.K, g.K, st)
+            x = self.pool_out
+        else:
+            self._conv(self.stem.desc, self.x0, self.stem.w, self.y_stem,
+                       stats=first_bn.fstats if training else None)
+            x = self.y_stem
+        for i, b in enumerate(self.blocks):
+            nxt = self.blocks[i + 1]["bn0"] if i + 1 < len(self.blocks) else self.final_bn
+            x = self._block_fwd(b, x, nxt, training)
+        self.x_final = x
+        fb = self.final_bn
+        hw = x.shape[1] * x.shape[2]
+        self._bn_finalize(fb, x.numel() // fb.C, training)
+        _nl.call("drn_bnrelu_avgpool", _p(x), _p(fb.ss), _p(self.pooled), self.B, hw, fb.C, st)
+        self._conv(self.dense_desc, self.pooled, self.dense_w, self.logits)
+
+    def _block_fwd(self, b: dict, x, next_bn: _BN, training: bool):
+        bn0 = b["bn0"]
+        b["x"] = x
+        self._bn_finalize(bn0, x.numel() // bn0.C, training)
+        self._bn_apply(bn0, x, b["a0"])
+        shortcut = x
+        if "proj" in b:
+            pj = b["proj"]
+            self._conv(pj.desc, b["a0"], pj.w, b["shortcut"])
+            shortcut = b["shortcut"]
+        h = b["a0"]
+        convs = b["convs"]
+        for i, c in enumerate(convs):
+            last = i + 1 == len(convs)
+            y = b["ys"][i]
+            if last:
+                self._conv(c.desc, h, c.w, y, side=shortcut, mode=EPI_RESADD,
+                           stats=next_bn.fstats if training else None)
+            else:
+                bn = b["bns"][i]
+                self._conv(c.desc, h, c.w, y, stats=bn.fstats if training else None)
+                self._bn_finalize(bn, y.numel() // bn.C, training)
+                self._bn_apply(bn, y, b["acts"][i])
+                h = b["acts"][i]
+        return b["ys"][-1]
+
+    # ---- loss ---------------------------------------------------------------------------------
+    def loss(self, with_grad: bool = True) -> None:
+        """scalars[0] += sum of per-example cross-entropies; correct += #hits; dlogits, dbias."""
+        _nl.call("drn_softmax_xent", _p(self.logits), self.kp, _p(self.dense_bias), _p(self.labels),
+                 self.B, self.spec.num_classes, 1.0 / self.B,
+                 _p(self.dlogits) if with_grad else 0, _p(self.dense_dbias) if with_grad else 0, 0,
+                 _p(self.scalars), _p(self.correct), self._st())
+
+    # ---- backward -----------------------------------------------------------------------------
+    def _get(self, like):
+        """Borrow a scratch buffer shaped like ``like`` (stream order makes reuse safe)."""
+        i = self._free.pop()
+        return i, self._scratch[i][: like.numel()].view(like.shape)
+
+    def _put(self, i: int) -> None:
+        self._free.append(i)
+
+    def backward(self) -> None:
+        s = self.spec
+        st = self._st()
+        self._free = list(range(len(self._scratch)))
+        # dense
+        self._conv(self.dense_ddesc, self.dlogits, self.dense_wd, self.d_pooled)
+        _nl.call("drn_conv_wgrad", ctypes.byref(self.dense_desc), _p(self.pooled), _p(self.dlogits),
+                 _p(self.dense_dw), 0, st)
+        # final BN + ReLU + average pool
+        fb = self.final_bn
+        x = self.x_final
+        Bn, H, W, C = x.shape
+        dm_i, dm = self._get(x)
+        _nl.call("drn_bn_bwd_mask_reduce", 0, _p(self.d_pooled), 3, Bn, H, W, 0, 0, 1.0 / (H * W),
+                 _p(x), _p(fb.ss), _p(dm), _p(fb.bstats), fb.bstats.stride(0), C, st)
+        g_i, g = self._get(x)
+        self._bn_bwd(fb, dm, x, None, g)
+        self._put(dm_i)
+        for b in reversed(self.blocks):
+            g_i, g = self._block_bwd(b, g_i, g)
+        # stem
+        if s.maxpool:
+            sg = self.stem.g
+            hp = self.pool_out.shape[1]
+            d_i, d_stem = self._get(self.y_stem)
+            _nl.call("drn_maxpool_bwd", _p(g), _p(self.pool_arg), _p(d_stem), self.B, sg.P, sg.Q,
+                     sg.K, 3, 2, 0, hp, hp, st)
+            self._put(g_i)
+            g_i, g = d_i, d_stem
+        self._wgrad(self.stem, self.x0, g)
+        self._put(g_i)
+        if self.stem_mask is not None:
+            _nl.call("drn_mul_inplace_f32", _p(self.stem.dw), _p(self.stem_mask),
+                     self.stem_mask.numel(), st)
+
+    def _bn_bwd(self, bn: _BN, dm, y, addend, out):
+        st = self._st()
+        count = y.numel() // bn.C
+        _nl.call("drn_bn_bwd_finalize", _p(bn.bstats), bn.bstats.stride(0), count, _p(bn.gamma),
+                 _p(bn.mi), _p(bn.dgamma), _p(bn.dbeta), _p(bn.coef), bn.C, st)
+        _nl.call("drn_bn_bwd_apply", _p(dm), _p(y), _p(bn.coef), _p(addend), _p(out), count, bn.C, st)
+
+    def _block_bwd(self, b: dict, g_i: int, g):
+        """g: gradient w.r.t. the block output (scratch[g_i]); returns (index, tensor) of the
+        gradient w.r.t. the block input."""
+        st = self._st()
+        convs, bns, ys, acts = b["convs"], b["bns"], b["ys"], b["acts"]
+        x, a0, bn0 = b["x"], b["a0"], b["bn0"]
+        dy_i, dy = g_i, g  # the residual add passes g unchanged to the last conv of the main path
+        for i in range(len(convs) - 1, 0, -1):
+            c, bn = convs[i], bns[i - 1]
+            y_prev, a_prev = ys[i - 1], acts[i - 1]
+            self._wgrad(c, a_prev, dy)
+            dm_i, dm = self._get(y_prev)
+            self._dgrad(c, dy, dm, side=y_prev, stats=bn.bstats, ss=bn.ss, mode=EPI_BNBWD)
+            if dy_i != g_i:
+                self._put(dy_i)
+            n_i, ndy = self._get(y_prev)
+            self._bn_bwd(bn, dm, y_prev, None, ndy)
+            self._put(dm_i)
+            dy_i, dy = n_i, ndy
+        c0 = convs[0]
+        self._wgrad(c0, a0, dy)
+        Bn, H, W, C = x.shape
+        if "proj" in b:
+            pj = b["proj"]
+            self._wgrad(pj, a0, g)
+            da_i, da = self._get(x)
+            self._dgrad(c0, dy, da)
+            if dy_i != g_i:
+                self._put(dy_i)
+            dm_i, dm = self._get(x)
+            if pj.g.stride == 1:
+                t_i, t = self._get(x)
+                self._conv(pj.dg_desc, g, pj.wd, t)
+                _nl.call("drn_bn_bwd_mask_reduce", _p(da), _p(t), 1, Bn, H, W, 0, 0, 0.0, _p(x),
+                         _p(bn0.ss), _p(dm), _p(bn0.bstats), bn0.bstats.stride(0), C, st)
+            else:
+                # compact data gradient of the 1x1/stride-s projection: a 1x1/1 conv over g
+                t_i = self._free.pop()
+                t = self._scratch[t_i][: Bn * pj.g.P * pj.g.Q * C].view(Bn, pj.g.P, pj.g.Q, C)
+                self._conv(b["proj_cdesc"], g, pj.wd, t)
+                _nl.call("drn_bn_bwd_mask_reduce", _p(da), _p(t), 2, Bn, H, W, pj.g.P, pj.g.Q, 0.0,
+                         _p(x), _p(bn0.ss), _p(dm), _p(bn0.bstats), bn0.bstats.stride(0), C, st)
+            self._put(da_i)
+            self._put(t_i)
+            self._put(g_i)
+            gin_i, gin = self._get(x)
+            self._bn_bwd(bn0, dm, x, None, gin)
+            self._put(dm_i)
+            return gin_i, gin
+        dm_i, dm = self._get(x)
+        self._dgrad(c0, dy, dm, side=x, stats=bn0.bstats, ss=bn0.ss, mode=EPI_BNBWD)
+        if dy_i != g_i:
+            self._put(dy_i)
+        gin_i, gin = self._get(x)
+        self._bn_bwd(bn0, dm, x, g, gin)
+        self._put(dm_i)
+        self._put(g_i)
+        return gin_i, gin
+
+    # ---- optimizer (single replica) -----------------------------------------------------------
+    def apply_gradients(self, want_l2: bool = True) -> None:
+        st = self._st()
+        _nl.call("drn_sgd_momentum", _p(self.master), _p(self.grad), _p(self.mom), _p(self.shadow),
+                 self.layout.total, _p(self.hyper), _p(self.scalars[1:]) if want_l2 else 0, 1, st)
+        self.prep_dgrad_weights()
+
+    def set_hyper(self, lr: float, momentum: float, weight_decay: float, grad_scale: float = 1.0):
+        self.hyper.copy_(torch.tensor([lr, momentum, weight_decay, grad_scale], dtype=torch.float32),
+                         non_blocking=True)
+
+    # ---- inputs ---------------------------------------------------------------------------------
+    def set_input_float(self, images_nhwc: torch.Tensor, labels: torch.Tensor) -> None:
+        """Load already-preprocessed float images [B,H,W,3] (test / oracle-comparison path; the
+        production path fills x0 with the device augmentation kernels in data/device_pipeline.py)."""
+        x = images_nhwc.to(self.device, torch.float32)
+        B, H, W, _ = x.shape
+        if self.spec.dataset == "imagenet":
+            # space-to-depth: channel = (dy*2+dx)*3 + c
+            x = x.view(B, H // 2, 2, W // 2, 2, 3).permute(0, 1, 3, 2, 4, 5).reshape(B, H // 2, W // 2, 12)
+            pad = 4
+        else:
+            pad = 13
+        x = torch.nn.functional.pad(x, (0, pad))
+        self.x0.copy_(x.to(torch.bfloat16))
+        self.labels.copy_(labels.to(self.device, torch.int32))
+
+    # ---- convenience: one full step (no graph) ----------------------------------------------------
+    def train_step_eager(self) -> None:
+        self.scalars.zero_()
+        self.correct.zero_()
+        self.forward(training=True)
+        self.loss(with_grad=True)
+        self.backward()
+        self.apply_gradients()

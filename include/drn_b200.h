@@ -64,6 +64,80 @@ int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const void* w, void
 int drn_conv_wgrad(const drn_conv_desc* desc, const void* x, const void* dy, float* dw,
                    int split_k, void* stream);
 
+
+/* ---------------------------------------------------------------------------------------------
+ * BatchNorm + ReLU (reference: batch_norm_relu, resnet_model_official.py:41-50; ops K5-K9)
+ * stats rows: [0] = per-channel sum, [1] = per-channel sum of squares (or sum dm*y in backward).
+ * scale_shift / mean_invstd are float2[C]; coef is float4[C].
+ * ------------------------------------------------------------------------------------------- */
+int drn_bn_finalize(const float* stats, int stats_ld, long long count, const float* gamma,
+                    const float* beta, float* run_mean /*nullable*/, float* run_var, float decay,
+                    float eps, void* scale_shift, void* mean_invstd, int C, void* stream);
+int drn_bn_inference_params(const float* gamma, const float* beta, const float* run_mean,
+                            const float* run_var, float eps, void* scale_shift, int C, void* stream);
+/* out = [relu](y*scale + shift [+ addend]) over an [M][C] bf16 tensor */
+int drn_bn_apply(const void* y, const void* scale_shift, const void* addend, void* out, long long M,
+                 int C, int relu, void* stream);
+int drn_bn_stats(const void* y, float* stats, int stats_ld, long long M, int C, void* stream);
+/* dm = (da [+ addend]) * [y*scale+shift > 0]; stats += (sum dm, sum dm*y).
+ * addend_kind: 0 none, 1 same shape, 2 compact stride-2 tensor [N,Ha,Wa,C] added at even pixels,
+ * 3 per-image vector [N][C] times bcast_scale (average-pool gradient; da may then be NULL). */
+int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int addend_kind, int N, int H, int W,
+                           int Ha, int Wa, float bcast_scale, const void* y, const void* scale_shift,
+                           void* dm, float* stats, int stats_ld, int C, void* stream);
+/* dgamma += sum dm*xhat, dbeta += sum dm (both nullable), coef = (A,B,C) of dy = A*dm + B*y + C */
+int drn_bn_bwd_finalize(const float* stats, int stats_ld, long long count, const float* gamma,
+                        const void* mean_invstd, float* dgamma, float* dbeta, void* coef, int C,
+                        void* stream);
+int drn_bn_bwd_apply(const void* dm, const void* y, const void* coef, const void* addend, void* dy,
+                     long long M, int C, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Pooling (reference resnet_model_official.py:314-316 max pool, :266-271/:334-339 average pool)
+ * ------------------------------------------------------------------------------------------- */
+int drn_maxpool_fwd(const void* x, void* out, void* argmax /*uint8 [N,P,Q,C]*/, int N, int H, int W,
+                    int C, int ksize, int stride, int pad_lo, int P, int Q, void* stream);
+int drn_maxpool_bwd(const void* dy, const void* argmax, void* dx, int N, int H, int W, int C,
+                    int ksize, int stride, int pad_lo, int P, int Q, void* stream);
+/* out[n][c] = mean_hw relu(y*scale + shift) */
+int drn_bnrelu_avgpool(const void* y, const void* scale_shift, void* out, int N, int HW, int C,
+                       void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Loss (reference resnet_model.py:77-82, resnet_cifar_main.py:270-272; ops K14-K16, K18)
+ * ------------------------------------------------------------------------------------------- */
+int drn_softmax_xent(const void* logits, int ld, const float* bias, const int* labels, int B,
+                     int classes, float grad_scale, void* dlogits, float* dbias, float* probs,
+                     float* loss_sum, int* correct, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Optimizer / weight layouts (reference resnet_model.py:85-99; ops K17, K19)
+ * ------------------------------------------------------------------------------------------- */
+/* hyper = device float[4] {lr, momentum, weight_decay, grad_scale}; n % 4 == 0 */
+int drn_sgd_momentum(float* master, float* grad, float* mom, void* shadow_bf16, long long n,
+                     const float* hyper, float* l2_sum, int zero_grad, void* stream);
+/* w_dgrad[c][R-1-r][S-1-s][k] = w_krsc[k][r][s][c] (bf16) */
+int drn_weight_prep_dgrad(const void* w_krsc, void* w_dgrad, int K, int R, int S, int C,
+                          void* stream);
+/* out[n, p*stride, q*stride, :] = dy[n, p, q, :], zero elsewhere; out is [N,U,V,C] */
+int drn_upsample_zero(const void* dy, void* out, int N, int P, int Q, int U, int V, int C,
+                      int stride, void* stream);
+int drn_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
+/* a[i] *= b[i] */
+int drn_mul_inplace_f32(float* a, const float* b, long long n, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Input pipelines on device (reference resnet_cifar_main.py:157-200, cifar_input.py:66-75,
+ * vgg_preprocessing.py; ops K13, K21, K22)
+ * ------------------------------------------------------------------------------------------- */
+int drn_cifar_augment(const void* records, int record_stride, int image_offset, void* out, int B,
+                      int pad, int training, unsigned long long seed, unsigned int step,
+                      long long index_base, int cpad, void* stream);
+int drn_imagenet_prep(const void* src, long long image_stride, int src_h, int src_w,
+                      const int* crop_yx_flip, void* out, int B, int crop, float mean_r,
+                      float mean_g, float mean_b, void* stream);
+int drn_resize_bilinear(const void* src, int sh, int sw, float* dst, int dh, int dw, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
