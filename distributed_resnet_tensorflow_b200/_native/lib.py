@@ -105,7 +105,23 @@ def check(status: int, what: str = "") -> None:
         raise RuntimeError(f"libdrn_b200 {what} failed: {msg}")
 
 
+_launch_count = 0
+
+
+def reset_launch_count() -> None:
+    global _launch_count
+    _launch_count = 0
+
+
+def launch_count() -> int:
+    """Number of kernel-launching C calls made through ``call`` since the last reset (every
+    ``drn_*`` launcher enqueues exactly one kernel of this library)."""
+    return _launch_count
+
+
 def call(name: str, *args) -> None:
+    global _launch_count
+    _launch_count += 1
     lib = load()
     fn = getattr(lib, name, None)
     if fn is None:
