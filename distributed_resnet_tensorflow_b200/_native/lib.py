@@ -58,6 +58,13 @@ _SIGNATURES = {
     "drn_cifar_augment": (_i, [_vp, _i, _i, _vp, _i, _i, _i, ctypes.c_ulonglong, ctypes.c_uint, _ll, _i, _vp]),
     "drn_imagenet_prep": (_i, [_vp, _ll, _i, _i, _vp, _vp, _i, _i, _f, _f, _f, _vp]),
     "drn_resize_bilinear": (_i, [_vp, _i, _i, _vp, _i, _i, _vp]),
+    "drn_comm_pad_bytes": (_i, []),
+    "drn_allreduce_f32": (_i, [_vp, _vp, _vp, _i, _i, _ll, _ll, _f, _i, _i, _vp]),
+    "drn_ps_update": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _ll, _ll, _vp, _vp, _i, _i, _vp]),
+    "drn_bcast_f32": (_i, [_vp, _vp, _i, _i, _i, _ll, _i, _i, _vp]),
+    "drn_comm_barrier": (_i, [_vp, _i, _i, _i, _vp]),
+    "drn_ipc_alloc": (_i, [ctypes.c_size_t, ctypes.POINTER(_vp), _vp]),
+    "drn_ipc_open": (_i, [_vp, ctypes.POINTER(_vp)]),
 }
 
 

@@ -203,7 +203,9 @@ class _Conv:
 
 
 class NativeResNet:
-    def __init__(self, spec: NetSpec, batch: int, device="cuda:0"):
+    def __init__(self, spec: NetSpec, batch: int, device="cuda:0", storage: Optional[dict] = None):
+        """``storage`` may supply pre-allocated ``grad`` (fp32) / ``shadow`` (bf16) arenas of at
+        least ``ParamLayout(spec).total`` elements - the collectives need them in symmetric memory."""
         if spec.version != 2:
             raise NotImplementedError("the native engine implements the reference's v2 networks; "
                                       "use --backend=torch for resnet_version=1")
@@ -215,9 +217,13 @@ class NativeResNet:
         n = self.layout.total
         dev = self.device
         self.master = torch.zeros(n, device=dev)
-        self.grad = torch.zeros(n, device=dev)
+        storage = storage or {}
+        self.grad = storage["grad"][:n] if "grad" in storage else torch.zeros(n, device=dev)
         self.mom = torch.zeros(n, device=dev)
-        self.shadow = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+        self.shadow = storage["shadow"][:n] if "shadow" in storage else \
+            torch.zeros(n, dtype=torch.bfloat16, device=dev)
+        assert self.grad.dtype == torch.float32 and self.shadow.dtype == torch.bfloat16
+        self.grad.zero_()
         self.hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0], device=dev)   # lr, momentum, wd, grad_scale
         self.scalars = torch.zeros(4, device=dev)       # [0] loss_sum, [1] l2_sum
         self.correct = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -502,9 +508,41 @@ class NativeResNet:
     def _put(self, i: int) -> None:
         self._free.append(i)
 
-    def backward(self) -> None:
+    def range_marks(self) -> List[int]:
+        """Arena offsets at which the stem, each block, and the head (final BN + dense) start."""
+        ent = self.layout.entries
+        marks = [0]
+        for b in self.spec.blocks:
+            marks.append(ent[f"{b.bns[0].name}/gamma"].offset)
+        marks.append(ent[f"{self.spec.final_bn.name}/gamma"].offset)
+        marks.append(self.layout.total)
+        return marks
+
+    def range_sequence(self) -> List[Tuple[int, int, bool]]:
+        """(lo, hi, last) arena ranges in the order backward() completes them."""
+        m = self.range_marks()
+        seq = [(m[-2], m[-1], False)]
+        for i in range(len(self.spec.blocks) - 1, -1, -1):
+            seq.append((m[i + 1], m[i + 2], False))
+        seq.append((m[0], m[1], True))
+        return seq
+
+    def bucket_ranges(self, bucket_elems: int) -> List[Tuple[int, int]]:
+        out, pend = [], []
+        for lo, hi, last in self.range_sequence():
+            pend.append((lo, hi))
+            lo_all, hi_all = min(p[0] for p in pend), max(p[1] for p in pend)
+            if last or hi_all - lo_all >= bucket_elems:
+                pend = []
+                out.append((lo_all, hi_all))
+        return out
+
+    def backward(self, range_hook=None) -> None:
+        """``range_hook(lo, hi, last)`` is called as soon as the gradient arena range [lo, hi) is
+        final (head first, stem last) so that collectives can overlap with the rest of backward."""
         s = self.spec
         st = self._st()
+        marks = self.range_marks()
         self._free = list(range(len(self._scratch)))
         # dense
         self._conv(self.dense_ddesc, self.dlogits, self.dense_wd, self.d_pooled)
@@ -520,8 +558,12 @@ class NativeResNet:
         g_i, g = self._get(x)
         self._bn_bwd(fb, dm, x, None, g)
         self._put(dm_i)
-        for b in reversed(self.blocks):
-            g_i, g = self._block_bwd(b, g_i, g)
+        if range_hook is not None:
+            range_hook(marks[-2], marks[-1], False)
+        for bi in range(len(self.blocks) - 1, -1, -1):
+            g_i, g = self._block_bwd(self.blocks[bi], g_i, g)
+            if range_hook is not None:
+                range_hook(marks[bi + 1], marks[bi + 2], False)
         # stem
         if s.maxpool:
             sg = self.stem.g
@@ -536,6 +578,8 @@ class NativeResNet:
         if self.stem_mask is not None:
             _nl.call("drn_mul_inplace_f32", _p(self.stem.dw), _p(self.stem_mask),
                      self.stem_mask.numel(), st)
+        if range_hook is not None:
+            range_hook(marks[0], marks[1], True)
 
     def _bn_bwd(self, bn: _BN, dm, y, addend, out):
         st = self._st()

@@ -258,11 +258,17 @@ def cifar_resnet(resnet_size: int = 50, num_classes: int = 10, version: int = 2)
                    tuple(blocks), final_bn, cout, hout)
 
 
-def imagenet_resnet(resnet_size: int = 50, num_classes: int = 1001, version: int = 2) -> NetSpec:
-    """resnet_model_official.py:281-366 - 7x7/2 stem, 3x3/2 max pool, 4 stages."""
-    if resnet_size not in IMAGENET_BLOCKS:
-        raise ValueError(f"Not a valid resnet_size: {resnet_size}")
-    kind, layers = IMAGENET_BLOCKS[resnet_size]
+def imagenet_resnet(resnet_size: int = 50, num_classes: int = 1001, version: int = 2,
+                    custom: Optional[Tuple[str, List[int]]] = None) -> NetSpec:
+    """resnet_model_official.py:281-366 - 7x7/2 stem, 3x3/2 max pool, 4 stages.
+    ``custom=(block kind, blocks per stage)`` builds the same generator with another depth
+    (imagenet_resnet_v2_generator accepts any ``layers``)."""
+    if custom is not None:
+        kind, layers = custom
+    else:
+        if resnet_size not in IMAGENET_BLOCKS:
+            raise ValueError(f"Not a valid resnet_size: {resnet_size}")
+        kind, layers = IMAGENET_BLOCKS[resnet_size]
     nm = _Namer()
     stem = ConvSpec(nm.conv_name(), 3, 64, 7, 2, 224)
     stem_bn = BNSpec(nm.bn_name(), 64) if version == 1 else None

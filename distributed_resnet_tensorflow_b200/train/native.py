@@ -33,7 +33,11 @@ class NativeTrainer:
         self.B = batch
         self.device = torch.device(device)
         torch.cuda.set_device(self.device)
-        self.engine = NativeResNet(spec, batch, device=device)
+        storage = None
+        if comm is not None:
+            from ..models.engine import ParamLayout
+            storage = comm.allocate(ParamLayout(spec).total)
+        self.engine = NativeResNet(spec, batch, device=device, storage=storage)
         self.weight_decay = weight_decay
         self.momentum = momentum
         self.seed = seed

@@ -138,6 +138,30 @@ int drn_imagenet_prep(const void* src, long long image_stride, int src_h, int sr
                       float mean_g, float mean_b, void* stream);
 int drn_resize_bilinear(const void* src, int sh, int sw, float* dst, int dh, int dw, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Collectives over NVLink / NVSwitch peer memory (reference call sites C1-C3).
+ * bufs / pads / grads / shadows are HOST arrays of `nranks` device pointers (index = rank) into
+ * symmetric allocations; every rank launches the same call. nblocks must match on all ranks.
+ * ------------------------------------------------------------------------------------------- */
+int drn_comm_pad_bytes(void);
+/* in-place: buf[offset:offset+count] = scale * sum over ranks (hvd.DistributedOptimizer, C2) */
+int drn_allreduce_f32(const void* const* bufs, void* mc_ptr /*nullable*/, const void* const* pads,
+                      int rank, int nranks, long long offset, long long count, float scale,
+                      int nblocks, int channel, void* stream);
+/* SyncReplicas parameter-server step (C1): owners (ranks < num_ps) average their gradient slice
+ * over all workers, apply L2 + momentum-SGD to master/mom and push bf16 weights to all workers */
+int drn_ps_update(const void* const* grads, const void* const* shadows, float* master, float* mom,
+                  const float* hyper, int rank, int nranks, int num_ps, long long offset,
+                  long long count, const void* const* pads, float* l2_sum, int nblocks, int channel,
+                  void* stream);
+/* copy root's buffer into every rank's buffer (BroadcastGlobalVariablesHook, C3) */
+int drn_bcast_f32(const void* const* bufs, const void* const* pads, int rank, int nranks, int root,
+                  long long count, int nblocks, int channel, void* stream);
+int drn_comm_barrier(const void* const* pads, int rank, int nranks, int channel, void* stream);
+/* start-up only; these two allocate / map device memory (CUDA IPC fallback for symmetric memory) */
+int drn_ipc_alloc(size_t bytes, void** out_ptr, void* out_handle64);
+int drn_ipc_open(const void* handle64, void** out_ptr);
+
 #ifdef __cplusplus
 }
 #endif

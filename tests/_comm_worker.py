@@ -1,0 +1,125 @@
+"""Multi-GPU worker launched by tests/test_comm_gpu.py through torch.distributed.run.
+Checks the in-kernel collectives against NCCL and a 2-replica training step against first
+principles.  Prints 'COMM_WORKER_OK' on rank 0 when every check passed."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    rank = int(os.environ["RANK"]); local = int(os.environ["LOCAL_RANK"]); world = int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    dist.init_process_group("nccl", device_id=torch.device(dev))
+    from distributed_resnet_tensorflow_b200._native import lib as nl
+    from distributed_resnet_tensorflow_b200.parallel.reducers import (CH_ALLREDUCE, AllreduceReducer,
+                                                                      ParameterServerReducer)
+    from distributed_resnet_tensorflow_b200.parallel.symm import SymmetricBuffer
+
+    provider = os.environ.get("DRN_SYMM", "auto")
+    # ---------------- raw allreduce vs NCCL, p2p and (if available) multicast -------------------
+    n = 1 << 20
+    red = AllreduceReducer(rank, world, dev, provider=provider)
+    store = red.allocate(n)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    for use_mc in (False, True):
+        if use_mc and not red.grad_buf.multicast_ptr:
+            continue
+        x = torch.randn(n, device=dev, generator=g)
+        store["grad"].copy_(x)
+        want = x.clone()
+        dist.all_reduce(want)
+        want /= world
+        torch.cuda.synchronize(); dist.barrier()
+        for (lo, cnt) in ((0, n // 2), (n // 2, n // 2)):
+            nl.call("drn_allreduce_f32", red.grad_buf.ptr_array(), red.grad_buf.mc() if use_mc else 0,
+                    red.pads.ptr_array(), rank, world, lo, cnt, 1.0 / world, 16, CH_ALLREDUCE,
+                    torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize(); dist.barrier()
+        err = (store["grad"] - want).abs().max().item()
+        assert err < 1e-5, ("allreduce", use_mc, err)
+        # every rank must hold bit-identical results
+        chk = store["grad"].double().sum().reshape(1)
+        allc = [torch.zeros_like(chk) for _ in range(world)]
+        dist.all_gather(allc, chk)
+        assert all(float(c) == float(allc[0]) for c in allc), "ranks disagree bitwise"
+        if rank == 0:
+            print(f"allreduce multicast={use_mc} provider={red.grad_buf.provider} maxerr={err:.2e}", flush=True)
+
+    # ---------------- end-to-end: 2-replica step == mean-gradient step --------------------------
+    from distributed_resnet_tensorflow_b200.models.init import init_variables
+    from distributed_resnet_tensorflow_b200.models.spec import build_spec
+    from distributed_resnet_tensorflow_b200.train.native import NativeTrainer
+    spec = build_spec("cifar10", 8)
+    B = 16
+    variables = init_variables(spec, seed=3)
+    rng = np.random.default_rng(7 + rank)
+    imgs = torch.from_numpy(rng.integers(0, 256, size=(B, 3072), dtype=np.uint8)).pin_memory()
+    labs = torch.from_numpy(rng.integers(0, 10, size=(B,), dtype=np.int32)).pin_memory()
+    results = {}
+    for mode in ("allreduce", "ps"):
+        comm = (AllreduceReducer(rank, world, dev, provider=provider) if mode == "allreduce"
+                else ParameterServerReducer(rank, world, dev, num_ps=max(1, world - 1) if world > 2 else world,
+                                            provider=provider))
+        tr = NativeTrainer(spec, B, device=dev, weight_decay=2e-4, comm=comm, use_graph=(mode == "allreduce"))
+        tr.import_variables(variables)
+        m = tr.train_step(imgs, labs, lr=0.1)
+        torch.cuda.synchronize(); dist.barrier()
+        if mode == "ps":
+            comm.gather_master(tr.engine)
+        w = tr.engine.master.clone()      # after ONE step (atomics make later steps diverge chaotically)
+        for _ in range(2):
+            m = tr.train_step(imgs, labs, lr=0.1)
+        torch.cuda.synchronize(); dist.barrier()
+        if mode == "ps":
+            comm.gather_master(tr.engine)
+        sh = tr.engine.shadow.float().clone()
+        # identical weights on every rank
+        for t, name in ((sh, "shadow"), (tr.engine.master.clone(), "master")):
+            ref = t.clone(); dist.broadcast(ref, 0)
+            assert torch.equal(ref, t), f"{mode}: {name} differs between ranks"
+        results[mode] = w
+        assert np.isfinite(m["cost"])
+        if rank == 0:
+            print(f"{mode}: 3 steps ok, cost={m['cost']:.4f}", flush=True)
+    # the two transports implement the same mathematics
+    diff = (results["allreduce"] - results["ps"]).abs().max().item()
+    if rank == 0:
+        print(f"allreduce-vs-ps max weight diff after one step: {diff:.3e}", flush=True)
+    assert diff < 1e-3, ("allreduce vs ps weights after one step", diff)
+
+    # single-replica reference: mean of the per-replica gradients applied once
+    tr1 = NativeTrainer(spec, B, device=dev, weight_decay=2e-4, comm=None, use_graph=False)
+    tr1.import_variables(variables)
+    e = tr1.engine
+    tr1.stage_batch(imgs, labs); torch.cuda.synchronize()
+    tr1._augment(0, True, 0)
+    e.scalars.zero_(); e.correct.zero_()
+    e.forward(True); e.loss(True); e.backward()
+    gmean = e.grad.clone(); dist.all_reduce(gmean); gmean /= world
+    e.grad.copy_(gmean)
+    tr1._set_lr(0.1)
+    e.apply_gradients()
+    comm = AllreduceReducer(rank, world, dev, provider=provider)
+    tr2 = NativeTrainer(spec, B, device=dev, weight_decay=2e-4, comm=comm, use_graph=False)
+    tr2.import_variables(variables)
+    tr2.train_step(imgs, labs, lr=0.1)
+    torch.cuda.synchronize()
+    d = (tr2.engine.master - e.master).abs().max().item()
+    if rank == 0:
+        print(f"allreduce dp step vs mean-gradient step: max weight diff {d:.3e}", flush=True)
+    assert d < 1e-3, ("dp step vs mean-gradient step", d)
+    dist.barrier()
+    if rank == 0:
+        print("COMM_WORKER_OK", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
