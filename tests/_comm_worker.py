@@ -97,6 +97,7 @@ def main():
     # single-replica reference: mean of the per-replica gradients applied once
     tr1 = NativeTrainer(spec, B, device=dev, weight_decay=2e-4, comm=None, use_graph=False)
     tr1.import_variables(variables)
+    tr1.rank, tr1.world = rank, world      # same augmentation stream as the data-parallel run
     e = tr1.engine
     tr1.stage_batch(imgs, labs); torch.cuda.synchronize()
     tr1._augment(0, True, 0)
@@ -104,6 +105,7 @@ def main():
     e.forward(True); e.loss(True); e.backward()
     gmean = e.grad.clone(); dist.all_reduce(gmean); gmean /= world
     e.grad.copy_(gmean)
+    tr1.world = 1
     tr1._set_lr(0.1)
     e.apply_gradients()
     comm = AllreduceReducer(rank, world, dev, provider=provider)
