@@ -67,6 +67,12 @@ WGRAD_CASES = [
     ("rn50 3x3 64->64 @56 N32", 32, 56, 64, 64, 3, 1, 1, 1),
     ("rn50 1x1 256->64 @56 N32", 32, 56, 256, 64, 1, 1, 0, 0),
     ("rn50 3x3 512->512 @7 N32", 32, 7, 512, 512, 3, 1, 1, 1),
+    ("3x3 c128 k128 h14 (1152 cols)", 4, 14, 128, 128, 3, 1, 1, 1),
+    ("3x3 s2 c128 k128 h28", 4, 28, 128, 128, 3, 2, 1, 1),
+    ("3x3 c32 k64 (288 cols)", 4, 16, 32, 64, 3, 1, 1, 1),
+    ("rn50 stem 4x4 c16 k64 @112 N32", 32, 112, 16, 64, 4, 1, 2, 1),
+    ("rn50 1x1 64->256 @56 N32", 32, 56, 64, 256, 1, 1, 0, 0),
+    ("rn50 1x1 2048->512 @7 N32", 32, 7, 2048, 512, 1, 1, 0, 0),
 ]
 
 

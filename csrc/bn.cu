@@ -71,26 +71,33 @@ __global__ void bn_inference_params_kernel(const float* __restrict__ gamma,
   scale_shift[c] = make_float2(sc, fmaf(-run_mean[c], sc, beta[c]));
 }
 
-// a = [relu](y*scale + shift [+ addend]); 8 channels per thread
+// a = [relu](y*scale + shift [+ addend]); 8 channels per thread.
+// The grid stride is a multiple of c8 (a power of two <= 256), so a thread always works on the
+// same 8 channels and keeps their coefficients in registers.
 __global__ void bn_apply_kernel(const BF8* __restrict__ y, const float2* __restrict__ scale_shift,
                                 const BF8* __restrict__ addend, BF8* __restrict__ out,
                                 long long n_vec, int c8, int relu) {
-  extern __shared__ float2 s_ss[];
-  for (int i = threadIdx.x; i < c8 * 8; i += blockDim.x) s_ss[i] = scale_shift[i];
-  __syncthreads();
   const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) {
-    const int cg = (int)(i % c8);
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cg = (int)(i % c8);
+  float2 ss[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) ss[k] = __ldg(scale_shift + cg * 8 + k);
+  for (; i < n_vec; i += stride) {
     float f[8];
     unpack8(y[i], f);
-    float ad[8];
-    if (addend != nullptr) unpack8(addend[i], ad);
+    if (addend != nullptr) {
+      float ad[8];
+      unpack8(addend[i], ad);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float2 ss = s_ss[cg * 8 + k];
-      float v = fmaf(f[k], ss.x, ss.y);
-      if (addend != nullptr) v += ad[k];
-      f[k] = relu ? fmaxf(v, 0.f) : v;
+      for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], ss[k].x, ss[k].y) + ad[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], ss[k].x, ss[k].y);
+    }
+    if (relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
     }
     out[i] = pack8(f);
   }
@@ -235,22 +242,24 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ stats, int stat
 __global__ void bn_bwd_apply_kernel(const BF8* __restrict__ dm, const BF8* __restrict__ y,
                                     const float4* __restrict__ coef, const BF8* __restrict__ addend,
                                     BF8* __restrict__ dy, long long n_vec, int c8) {
-  extern __shared__ float4 s_coef[];
-  for (int i = threadIdx.x; i < c8 * 8; i += blockDim.x) s_coef[i] = coef[i];
-  __syncthreads();
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) {
-    const int cg = (int)(i % c8);
-    float g[8], yy[8], ad[8];
+  const long long stride = (long long)gridDim.x * blockDim.x;  // multiple of c8: channels stay fixed
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cg = (int)(i % c8);
+  float4 cf[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) cf[k] = __ldg(coef + cg * 8 + k);
+  for (; i < n_vec; i += stride) {
+    float g[8], yy[8];
     unpack8(dm[i], g);
     unpack8(y[i], yy);
-    if (addend != nullptr) unpack8(addend[i], ad);
+    if (addend != nullptr) {
+      float ad[8];
+      unpack8(addend[i], ad);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float4 cf = s_coef[cg * 8 + k];
-      float v = fmaf(cf.x, g[k], fmaf(cf.y, yy[k], cf.z));
-      if (addend != nullptr) v += ad[k];
-      g[k] = v;
+      for (int k = 0; k < 8; ++k) g[k] = fmaf(cf[k].x, g[k], fmaf(cf[k].y, yy[k], cf[k].z)) + ad[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = fmaf(cf[k].x, g[k], fmaf(cf[k].y, yy[k], cf[k].z));
     }
     dy[i] = pack8(g);
   }
@@ -298,9 +307,9 @@ extern "C" int drn_bn_inference_params(const float* gamma, const float* beta, co
 
 extern "C" int drn_bn_apply(const void* y, const void* scale_shift, const void* addend, void* out,
                             long long M, int C, int relu, void* stream) {
-  DRN_REQUIRE(C % 8 == 0 && C <= 4096, "bn_apply: C=%d must be a multiple of 8, <= 4096", C);
+  if (int e = check_c(C, "bn_apply")) return e;
   const long long n_vec = M * (C / 8);
-  bn_apply_kernel<<<ew_grid(n_vec), kThreads, C * sizeof(float2), (cudaStream_t)stream>>>(
+  bn_apply_kernel<<<ew_grid(n_vec), kThreads, 0, (cudaStream_t)stream>>>(
       (const BF8*)y, (const float2*)scale_shift, (const BF8*)addend, (BF8*)out, n_vec, C / 8, relu);
   DRN_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -351,9 +360,9 @@ extern "C" int drn_bn_bwd_finalize(const float* stats, int stats_ld, long long c
 
 extern "C" int drn_bn_bwd_apply(const void* dm, const void* y, const void* coef, const void* addend,
                                 void* dy, long long M, int C, void* stream) {
-  DRN_REQUIRE(C % 8 == 0 && C <= 2048, "bn_bwd_apply: C=%d must be a multiple of 8, <= 2048", C);
+  if (int e = check_c(C, "bn_bwd_apply")) return e;
   const long long n_vec = M * (C / 8);
-  bn_bwd_apply_kernel<<<ew_grid(n_vec), kThreads, C * sizeof(float4), (cudaStream_t)stream>>>(
+  bn_bwd_apply_kernel<<<ew_grid(n_vec), kThreads, 0, (cudaStream_t)stream>>>(
       (const BF8*)dm, (const BF8*)y, (const float4*)coef, (const BF8*)addend, (BF8*)dy, n_vec,
       C / 8);
   DRN_CHECK_CUDA(cudaGetLastError());

@@ -28,28 +28,28 @@ struct WgradParams {
   int chunks_total;     // ceil(M / 64)
   int chunks_per_split;
   int splits;
-  int co_tiles, ci_tiles, taps;
+  int co_tiles, col_tiles;
+  int cols_per_cta;     // columns of the flattened (tap, channel) axis handled by one CTA (<= 256)
+  int cols_total;       // R*S*C
   int S;
   int PQ, Q;
   int stride, pad;
   int Kout, C;
-  long long dw_row_stride;  // R*S*C
   float* dw;
 };
 
-template <int CWA, int CWB, int NB>
+template <int CWA, int CWB>
 struct WCfg {
+  static constexpr int kMaxCols = 256;
   static constexpr int kRBA = CWA * 2, kRBB = CWB * 2;
-  static constexpr int kABoxes = 128 / CWA, kBBoxes = NB / CWB;
+  static constexpr int kABoxes = 128 / CWA, kMaxBBoxes = kMaxCols / CWB;
   static constexpr int kABoxBytes = kPix * kRBA, kBBoxBytes = kPix * kRBB;
-  static constexpr int kABytes = kABoxes * kABoxBytes;  // 16 KB
-  static constexpr int kBBytesRaw = kBBoxes * kBBoxBytes;
-  static constexpr int kBBytes = (kBBytesRaw + 1023) / 1024 * 1024;
+  static constexpr int kABytes = kABoxes * kABoxBytes;          // 16 KB
+  static constexpr int kBBytes = kMaxBBoxes * kBBoxBytes;       // 32 KB
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStagesRaw = (200 * 1024) / kStageBytes;
-  static constexpr int kStages = kStagesRaw > kMaxStages ? kMaxStages : kStagesRaw;
+  static constexpr int kStages = 4;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 1024;
-  static constexpr int kTmemCols = NB <= 32 ? 32 : NB <= 64 ? 64 : NB <= 128 ? 128 : 256;
+  static constexpr int kTmemCols = 256;
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -58,11 +58,15 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
                : "memory");
 }
 
-template <int CWA, int CWB, int NB>
+// One CTA: rows = 128 output channels, columns = a <=256-wide window of the flattened
+// (filter tap, input channel) axis - which is exactly the memory order of dW[k][r][s][c] - and a
+// range of output pixels as the reduction.  Every column box of CWB channels is one im2col TMA
+// load (its own tap), so the dY tile is fetched once for up to 16 taps.
+template <int CWA, int CWB>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_constant__ CUtensorMap tmapX,
                   const WgradParams p) {
-  using C_ = WCfg<CWA, CWB, NB>;
+  using C_ = WCfg<CWA, CWB>;
   constexpr int kStages = C_::kStages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -83,12 +87,12 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
   int u = blockIdx.x;
   const int split = u % p.splits;
   u /= p.splits;
-  const int ci_tile = u % p.ci_tiles;
-  u /= p.ci_tiles;
-  const int co_tile = u % p.co_tiles;
-  const int tap = u / p.co_tiles;
-  const int r = tap / p.S;
-  const int s = tap - r * p.S;
+  const int col_tile = u % p.col_tiles;
+  const int co_tile = u / p.col_tiles;
+  const int n0 = col_tile * p.cols_per_cta;
+  int ncols = p.cols_total - n0;
+  if (ncols > p.cols_per_cta) ncols = p.cols_per_cta;
+  const int nboxes = ncols / CWB;
   const int chunk_begin = split * p.chunks_per_split;
   int chunk_end = chunk_begin + p.chunks_per_split;
   if (chunk_end > p.chunks_total) chunk_end = p.chunks_total;
@@ -118,26 +122,36 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
       if (elect_one()) {
         int stage = 0;
         uint32_t phase = 0;
+        const uint32_t tx_bytes = C_::kABytes + nboxes * C_::kBBoxBytes;
         for (int ch = chunk_begin; ch < chunk_end; ++ch) {
           const int m0 = ch * kPix;
           const int img = m0 / p.PQ;
           const int rem = m0 - img * p.PQ;
           const int op = rem / p.Q;
           const int oq = rem - op * p.Q;
+          const int w0 = oq * p.stride - p.pad, h0 = op * p.stride - p.pad;
           mbar_wait(empty_bar(stage), phase ^ 1, 0x110 + stage);
           const uint32_t a_dst = sStages + stage * C_::kStageBytes;
           const uint32_t b_dst = a_dst + C_::kABytes;
-          mbar_arrive_expect_tx(full_bar(stage), C_::kABytes + C_::kBBytesRaw);
+          mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
 #pragma unroll
           for (int i = 0; i < C_::kABoxes; ++i)
             tma_load_2d(a_dst + i * C_::kABoxBytes, &tmapDY, full_bar(stage),
                         co_tile * 128 + i * CWA, m0);
-#pragma unroll
-          for (int i = 0; i < C_::kBBoxes; ++i)
-            tma_load_im2col_4d(b_dst + i * C_::kBBoxBytes, &tmapX, full_bar(stage),
-                               ci_tile * NB + i * CWB, oq * p.stride - p.pad,
-                               op * p.stride - p.pad, img, static_cast<uint16_t>(s),
-                               static_cast<uint16_t>(r));
+          int flat = n0;
+          int tap = flat / p.C;
+          int c0 = flat - tap * p.C;
+          for (int i = 0; i < nboxes; ++i) {
+            const int r = tap / p.S;
+            const int s = tap - r * p.S;
+            tma_load_im2col_4d(b_dst + i * C_::kBBoxBytes, &tmapX, full_bar(stage), c0, w0, h0, img,
+                               static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+            c0 += CWB;
+            if (c0 >= p.C) {
+              c0 = 0;
+              ++tap;
+            }
+          }
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
@@ -146,7 +160,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
       }
     } else if (warp == 1) {
       if (elect_one()) {
-        constexpr uint32_t kIdesc = make_idesc_bf16(128, NB, 1, 1);
+        const uint32_t idesc = make_idesc_bf16(128, ncols, 1, 1);
         constexpr uint32_t kLayA = umma_layout_for_swizzle_bytes(C_::kRBA);
         constexpr uint32_t kLayB = umma_layout_for_swizzle_bytes(C_::kRBB);
         int stage = 0;
@@ -164,7 +178,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
                                                    8 * C_::kRBA, kLayA);
             const uint64_t b_desc = make_smem_desc(b_addr + kk * 16 * C_::kRBB, C_::kBBoxBytes,
                                                    8 * C_::kRBB, kLayB);
-            umma_f16(tmem_base, a_desc, b_desc, kIdesc, (ch | kk) != 0 ? 1u : 0u);
+            umma_f16(tmem_base, a_desc, b_desc, idesc, (ch | kk) != 0 ? 1u : 0u);
           }
           umma_commit(empty_bar(stage));
           if (++stage == kStages) {
@@ -181,31 +195,18 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
       const int co = co_tile * 128 + row;
       mbar_wait(tfull_bar, 0, 0x140);
       tc_fence_after();
-      float* dst_row = p.dw + (long long)co * p.dw_row_stride + (long long)tap * p.C + ci_tile * NB;
-      constexpr int kStep = NB >= 32 ? 32 : 16;
+      float* dst_row = p.dw + (long long)co * p.cols_total + n0;
 #pragma unroll 1
-      for (int c0 = 0; c0 < NB; c0 += kStep) {
+      for (int c0 = 0; c0 < ncols; c0 += 16) {
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + c0;
-        if constexpr (kStep == 32) {
-          uint32_t v[32];
-          tmem_ld_32x32(taddr, v);
-          tmem_ld_wait();
-          if (co < p.Kout) {
+        uint32_t v[16];
+        tmem_ld_32x16(taddr, v);
+        tmem_ld_wait();
+        if (co < p.Kout) {
 #pragma unroll
-            for (int i = 0; i < 32; i += 4)
-              red_add_v4(dst_row + c0 + i, __uint_as_float(v[i]), __uint_as_float(v[i + 1]),
-                         __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
-          }
-        } else {
-          uint32_t v[16];
-          tmem_ld_32x16(taddr, v);
-          tmem_ld_wait();
-          if (co < p.Kout) {
-#pragma unroll
-            for (int i = 0; i < 16; i += 4)
-              red_add_v4(dst_row + c0 + i, __uint_as_float(v[i]), __uint_as_float(v[i + 1]),
-                         __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
-          }
+          for (int i = 0; i < 16; i += 4)
+            red_add_v4(dst_row + c0 + i, __uint_as_float(v[i]), __uint_as_float(v[i + 1]),
+                       __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
         }
       }
     }
@@ -219,17 +220,22 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
   }
 }
 
-template <int CWA, int CWB, int NB>
+template <int CWA, int CWB>
 int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* dw, int split_k,
                  cudaStream_t stream) {
-  using C_ = WCfg<CWA, CWB, NB>;
+  using C_ = WCfg<CWA, CWB>;
   const long long M = 1LL * d.N * d.P * d.Q;
   WgradParams p;
   p.chunks_total = (int)((M + kPix - 1) / kPix);
   p.co_tiles = (d.K + 127) / 128;
-  p.ci_tiles = d.C / NB;
-  p.taps = d.R * d.S;
-  const int units = p.taps * p.co_tiles * p.ci_tiles;
+  p.cols_total = d.R * d.S * d.C;
+  int tiles = (p.cols_total + C_::kMaxCols - 1) / C_::kMaxCols;
+  int cols = (p.cols_total + tiles - 1) / tiles;
+  cols = (cols + CWB - 1) / CWB * CWB;
+  if (cols % 16 != 0) cols = (cols + 15) / 16 * 16;
+  p.cols_per_cta = cols;
+  p.col_tiles = (p.cols_total + cols - 1) / cols;
+  const int units = p.col_tiles * p.co_tiles;
   int splits = split_k;
   if (splits <= 0) {
     // ~2 waves of CTAs, but keep at least 8 chunks (512 pixels) per CTA
@@ -249,7 +255,6 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
   p.pad = d.pad_lo;
   p.Kout = d.K;
   p.C = d.C;
-  p.dw_row_stride = 1LL * d.R * d.S * d.C;
   p.dw = dw;
 
   CUtensorMap tDY, tX;
@@ -260,13 +265,13 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
     return e;
   static bool attr_set = false;
   if (!attr_set) {
-    DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<CWA, CWB, NB>,
+    DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<CWA, CWB>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         C_::kSmemBytes));
     attr_set = true;
   }
   const int grid = units * splits;
-  conv_wgrad_kernel<CWA, CWB, NB><<<grid, kThreads, C_::kSmemBytes, stream>>>(tDY, tX, p);
+  conv_wgrad_kernel<CWA, CWB><<<grid, kThreads, C_::kSmemBytes, stream>>>(tDY, tX, p);
   DRN_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -274,11 +279,9 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
 template <int CWA>
 int dispatch_b(const drn_conv_desc& d, const void* x, const void* dy, float* dw, int split_k,
                cudaStream_t st) {
-  if (d.C == 16) return launch_wgrad<CWA, 16, 16>(d, x, dy, dw, split_k, st);
-  if (d.C == 32) return launch_wgrad<CWA, 32, 32>(d, x, dy, dw, split_k, st);
-  if (d.C % 256 == 0) return launch_wgrad<CWA, 64, 256>(d, x, dy, dw, split_k, st);
-  if (d.C % 128 == 0) return launch_wgrad<CWA, 64, 128>(d, x, dy, dw, split_k, st);
-  return launch_wgrad<CWA, 64, 64>(d, x, dy, dw, split_k, st);
+  if (d.C == 16) return launch_wgrad<CWA, 16>(d, x, dy, dw, split_k, st);
+  if (d.C == 32) return launch_wgrad<CWA, 32>(d, x, dy, dw, split_k, st);
+  return launch_wgrad<CWA, 64>(d, x, dy, dw, split_k, st);
 }
 
 }  // namespace

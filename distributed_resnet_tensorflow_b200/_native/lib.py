@@ -58,6 +58,8 @@ _SIGNATURES = {
     "drn_cifar_augment": (_i, [_vp, _i, _i, _vp, _i, _i, _i, ctypes.c_ulonglong, ctypes.c_uint, _ll, _i, _vp]),
     "drn_imagenet_prep": (_i, [_vp, _ll, _i, _i, _vp, _vp, _i, _i, _f, _f, _f, _vp]),
     "drn_resize_bilinear": (_i, [_vp, _i, _i, _vp, _i, _i, _vp]),
+    "drn_crc32c": (ctypes.c_uint32, [_vp, ctypes.c_size_t, ctypes.c_uint32]),
+    "drn_tfrecord_index": (_ll, [_vp, ctypes.c_size_t, _vp, _vp, _ll, _i]),
     "drn_comm_pad_bytes": (_i, []),
     "drn_allreduce_f32": (_i, [_vp, _vp, _vp, _i, _i, _ll, _ll, _f, _i, _i, _vp]),
     "drn_ps_update": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _ll, _ll, _vp, _vp, _i, _i, _vp]),

@@ -139,6 +139,14 @@ int drn_imagenet_prep(const void* src, long long image_stride, int src_h, int sr
 int drn_resize_bilinear(const void* src, int sh, int sw, float* dst, int dh, int dw, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Host utilities (no GPU): CRC-32C (Castagnoli) used by TensorBundle checkpoints, TFRecord files
+ * and TensorBoard event files (the reference gets these from TensorFlow's runtime).
+ * ------------------------------------------------------------------------------------------- */
+uint32_t drn_crc32c(const void* data, size_t n, uint32_t crc);
+long long drn_tfrecord_index(const uint8_t* buf, size_t n, uint64_t* offsets, uint64_t* lengths,
+                             long long max_records, int verify);
+
+/* ---------------------------------------------------------------------------------------------
  * Collectives over NVLink / NVSwitch peer memory (reference call sites C1-C3).
  * bufs / pads / grads / shadows are HOST arrays of `nranks` device pointers (index = rank) into
  * symmetric allocations; every rank launches the same call. nblocks must match on all ranks.
