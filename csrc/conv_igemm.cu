@@ -8,8 +8,8 @@
 // * B operand (filters, [Cout][R*S*C] bf16) is fetched with tiled TMA.
 // * Accumulators live in TMEM, double-buffered, so the epilogue of tile i overlaps the main loop
 //   of tile i+1.  One elected thread issues the MMAs.
-// * The epilogue (4 warps) drains TMEM in 64-column chunks through swizzled smem and TMA-stores
-//   bf16.  It optionally fuses
+// * The epilogue (two groups of 4 warps, alternating 32-column chunks, double-buffered) drains TMEM through swizzled
+//   smem and TMA-stores bf16.  It optionally fuses
 //     - a residual add (ResNet shortcut;  reference resnet_model_official.py:130,175),
 //     - per-channel sum / sum-of-squares of the stored tensor (the batch statistics of the NEXT
 //       BatchNorm; reference resnet_model_official.py:45-48),
@@ -30,7 +30,7 @@ namespace {
 
 constexpr int kBM = 128;            // output pixels per tile (UMMA M)
 constexpr int kEpiBufs = 2;         // double-buffered epilogue chunk buffers
-constexpr int kNumThreads = 256;    // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps4-7 epilogue
+constexpr int kNumThreads = 384;    // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4-11 epilogue (2 groups)
 constexpr int kEpiThreads = 128;
 constexpr int kMaxStages = 8;
 
@@ -42,6 +42,8 @@ struct ConvParams {
   int S;           // filter width
   int PQ, Q;       // output plane / width
   int stride_h, stride_w, pad_h, pad_w;
+  int n_stages;    // smem pipeline depth (<= kMaxStages)
+  int n_res;       // side-input ring depth per epilogue group (0 in PLAIN mode)
   int mode;        // DRN_EPI_*
   int want_stats;  // accumulate per-channel sums into stats[0][*], stats[1][*]
   int n_valid;     // Cout (columns >= n_valid are padding)
@@ -50,29 +52,35 @@ struct ConvParams {
   const float2* bn_scale_shift;  // [Cout] (scale, shift) of the BN whose backward mask is applied
 };
 
+constexpr int kMaxRes = 8;          // side-input ring depth per epilogue group (upper bound)
+constexpr int kSmemBudget = 226 * 1024;
+
 template <int KC, int BN>
 struct Cfg {
   static constexpr int kABytes = kBM * KC * 2;
   static constexpr int kBBytesRaw = BN * KC * 2;
   static constexpr int kBBytes = (kBBytesRaw + 1023) / 1024 * 1024;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kCW = BN < 64 ? BN : 64;       // epilogue chunk width (columns)
+  static constexpr int kCW = BN < 32 ? BN : 32;       // epilogue chunk width (columns)
   static constexpr int kChunks = BN / kCW;
   static constexpr int kRowBytes = kCW * 2;            // bytes per staged row (= swizzle span)
-  static constexpr int kChunkBytes = kBM * kRowBytes;  // <= 16 KB
-  static constexpr int kEpiBytes = 2 * kEpiBufs * kChunkBytes;  // out[2] + res[2]
-  static constexpr int kAuxBytes = 2048 + 1024;        // scale/shift cache (256 * 8) + barriers
-  static constexpr int kBudget = 222 * 1024;
-  static constexpr int kStagesRaw = (kBudget - kEpiBytes - kAuxBytes) / kStageBytes;
-  static constexpr int kStages = kStagesRaw > kMaxStages ? kMaxStages : kStagesRaw;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kAuxBytes + 1024;
+  static constexpr int kChunkBytes = kBM * kRowBytes;  // <= 8 KB
+  static constexpr int kOutBytes = 2 * kEpiBufs * kChunkBytes;   // 2 groups x out[2]
+  static constexpr int kAuxBytes = 4096 + 2048 + 1024;  // 2 x scale/shift cache, 2 x stats scratch, barriers
   static constexpr int kTmemColsRaw = 2 * BN;
   static constexpr int kTmemCols = kTmemColsRaw <= 32    ? 32
                                    : kTmemColsRaw <= 64  ? 64
                                    : kTmemColsRaw <= 128 ? 128
                                    : kTmemColsRaw <= 256 ? 256
                                                          : 512;
-  static_assert(kStages >= 2, "pipeline too shallow");
+  // smem plan for a given side-input ring depth (per group)
+  static constexpr int stages_for(int n_res) {
+    int s = (kSmemBudget - 1024 - kAuxBytes - kOutBytes - 2 * n_res * kChunkBytes) / kStageBytes;
+    return s > kMaxStages ? kMaxStages : s;
+  }
+  static constexpr int smem_for(int n_res, int stages) {
+    return 1024 + kAuxBytes + kOutBytes + 2 * n_res * kChunkBytes + stages * kStageBytes;
+  }
 };
 
 template <int KC, int BN>
@@ -81,7 +89,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                   const __grid_constant__ CUtensorMap tmapC, const __grid_constant__ CUtensorMap tmapR,
                   const ConvParams p) {
   using C_ = Cfg<KC, BN>;
-  constexpr int kStages = C_::kStages;
+  const int kStages = p.n_stages;
   constexpr int kCW = C_::kCW;
   constexpr int kRowBytes = C_::kRowBytes;
 
@@ -92,22 +100,28 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 
   const uint32_t sStages = smem_base;
   const uint32_t sOut = sStages + kStages * C_::kStageBytes;
-  const uint32_t sRes = sOut + kEpiBufs * C_::kChunkBytes;
-  const uint32_t sAux = sRes + kEpiBufs * C_::kChunkBytes;
-  float2* sScaleShift = reinterpret_cast<float2*>(smem_gen + (sAux - smem_base));  // 256 entries
-  const uint32_t sBar = sAux + 2048;
+  const uint32_t sRes = sOut + C_::kOutBytes;
+  const uint32_t sAux = sRes + 2 * p.n_res * C_::kChunkBytes;
+  float2* sScaleShift = reinterpret_cast<float2*>(smem_gen + (sAux - smem_base));  // 2 x 256 entries
+  const uint32_t sBar = sAux + 4096 + 2048;
   // barrier map (8 bytes each)
   auto full_bar = [&](int s) { return sBar + 8u * s; };
   auto empty_bar = [&](int s) { return sBar + 8u * (kMaxStages + s); };
   auto tfull_bar = [&](int b) { return sBar + 8u * (2 * kMaxStages + b); };
   auto tempty_bar = [&](int b) { return sBar + 8u * (2 * kMaxStages + 2 + b); };
-  auto res_bar = [&](int b) { return sBar + 8u * (2 * kMaxStages + 4 + b); };
-  const uint32_t sTmemPtr = sBar + 8u * (2 * kMaxStages + 8);
+  auto res_bar = [&](int b) { return sBar + 8u * (2 * kMaxStages + 4 + b); };  // b in [0, 2*kMaxRes)
+  const uint32_t sTmemPtr = sBar + 8u * (2 * kMaxStages + 4 + 2 * kMaxRes);
   volatile uint32_t* tmem_ptr_gen =
       reinterpret_cast<volatile uint32_t*>(smem_gen + (sTmemPtr - smem_base));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+
+  // Each CTA owns a contiguous range of the n-major tile order, so it crosses a column-tile
+  // boundary (statistics flush, scale/shift reload) at most once or twice.
+  const int t_q = p.total_tiles / (int)gridDim.x, t_r = p.total_tiles % (int)gridDim.x;
+  const int t_begin = (int)blockIdx.x * t_q + ((int)blockIdx.x < t_r ? (int)blockIdx.x : t_r);
+  const int t_end = t_begin + t_q + ((int)blockIdx.x < t_r ? 1 : 0);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmapA);
@@ -122,9 +136,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(tfull_bar(b), 1);
-      mbar_init(tempty_bar(b), kEpiThreads);
-      mbar_init(res_bar(b), 1);
+      mbar_init(tempty_bar(b), kEpiThreads * C_::kChunks);  // one arrival per thread per chunk
     }
+    for (int b = 0; b < 2 * kMaxRes; ++b) mbar_init(res_bar(b), 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -141,7 +155,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+      for (int t = t_begin; t < t_end; ++t) {
         const int n_tile = t / p.m_tiles;
         const int m_tile = t - n_tile * p.m_tiles;
         const int m0 = m_tile * kBM;
@@ -180,7 +194,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+      for (int t = t_begin; t < t_end; ++t) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1, 0x30 + acc);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -208,176 +222,243 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
       }
     }
   } else if (warp >= 4) {
-    // ======================= epilogue =======================
-    const int et = threadIdx.x - 128;       // 0..127
-    const int quad = warp & 3;              // TMEM lane quadrant this warp may read
-    const int row = quad * 32 + lane;       // tile row == TMEM lane
+    // ======================= epilogue: two groups of 4 warps =======================
+    // A tile is drained in kChunks column chunks of kCW (<= 32) columns.  With kChunks >= 2 group
+    // 0 takes the even chunks of every tile and group 1 the odd ones; with a single chunk per
+    // tile the groups alternate tiles.  Each group owns two staging buffers, a ring of side-input
+    // buffers and a named barrier, so one group's TMA waits overlap the other's arithmetic.
+    const int grp = (warp - 4) >> 2;
+    const int et = threadIdx.x - 128 - grp * kEpiThreads;  // 0..127 inside the group
+    const int quad = warp & 3;               // TMEM lane quadrant this warp may read
+    const int row = quad * 32 + lane;        // tile row == TMEM lane
     const bool leader = (et == 0);
     const bool has_res = (p.mode != DRN_EPI_PLAIN);
-    constexpr int kTPC = kEpiThreads / kCW;   // threads per column in the statistics pass
-    constexpr int kRowsPerThread = kBM / kTPC;
-    const int scol = et % kCW;                // my column inside a chunk
-    const int srow0 = (et / kCW) * kRowsPerThread;
-
-    float acc_s1[C_::kChunks], acc_s2[C_::kChunks];
+    const uint32_t bar_id = 1 + grp;
+    const uint32_t out_base = sOut + grp * kEpiBufs * C_::kChunkBytes;
+    const uint32_t res_base = sRes + grp * p.n_res * C_::kChunkBytes;
+    const uint32_t n_res = p.n_res;
+    float2* my_ss = sScaleShift + grp * 256;
+    float* my_red = reinterpret_cast<float*>(sScaleShift + 512) + grp * 256;  // [2][kHalf*kCW]
+    constexpr int kHalf = C_::kChunks >= 2 ? C_::kChunks / 2 : 1;  // chunks per tile per group
+    // swizzled byte offsets of my row's 16-byte pieces inside a staging buffer (chunk independent)
+    uint32_t row_off[kRowBytes / 16];
 #pragma unroll
-    for (int j = 0; j < C_::kChunks; ++j) acc_s1[j] = acc_s2[j] = 0.f;
+    for (int c16 = 0; c16 < kRowBytes / 16; ++c16)
+      row_off[c16] = swz_off(row * kRowBytes + c16 * 16, kRowBytes);
+    // statistics pass: thread = (8-column group scg, row slot srs), kNcg rows per thread
+    constexpr int kNcg = kCW / 8;
+    constexpr int kNrs = kEpiThreads / kNcg;
+    const int scg = et % kNcg;
+    const int srs = et / kNcg;
+    uint32_t st_off[kNcg];
+#pragma unroll
+    for (int i = 0; i < kNcg; ++i)
+      st_off[i] = swz_off((srs + kNrs * i) * kRowBytes + scg * 16, kRowBytes);
+    float acc1[kHalf][8], acc2[kHalf][8];
+#pragma unroll
+    for (int a = 0; a < kHalf; ++a)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc1[a][k] = acc2[a][k] = 0.f;
     int cur_n_tile = -1;
+
+    // Reduce the per-thread partial sums over the group (shuffles, then shared-memory atomics)
+    // and add one value per channel to the global statistics.
+    auto flush_stats = [&](int n_tile) {
+      if (!p.want_stats || n_tile < 0) return;
+      for (int i = et; i < 2 * kHalf * kCW; i += kEpiThreads) my_red[i] = 0.f;
+      named_bar_sync(bar_id, kEpiThreads);
+#pragma unroll
+      for (int a = 0; a < kHalf; ++a) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float v1 = acc1[a][k], v2 = acc2[a][k];
+#pragma unroll
+          for (int o = kNcg; o < 32; o <<= 1) {
+            v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+            v2 += __shfl_xor_sync(0xffffffffu, v2, o);
+          }
+          if (lane < kNcg) {
+            atomicAdd(my_red + a * kCW + scg * 8 + k, v1);
+            atomicAdd(my_red + kHalf * kCW + a * kCW + scg * 8 + k, v2);
+          }
+          acc1[a][k] = acc2[a][k] = 0.f;
+        }
+      }
+      named_bar_sync(bar_id, kEpiThreads);
+      for (int i = et; i < 2 * kHalf * kCW; i += kEpiThreads) {
+        const int which = i / (kHalf * kCW);
+        const int r = i - which * kHalf * kCW;
+        const int a = r / kCW;
+        const int j = C_::kChunks >= 2 ? a * 2 + grp : 0;
+        const int col = n_tile * BN + j * kCW + (r - a * kCW);
+        if (col < p.n_valid) atomicAdd(p.stats + which * p.stats_ld + col, my_red[i]);
+      }
+      named_bar_sync(bar_id, kEpiThreads);
+    };
+    // (tile, chunk) of the idx-th chunk this group processes
+    auto locate = [&](uint32_t idx, int& tile, int& chunk) {
+      const uint32_t gg = idx * 2 + grp;
+      tile = t_begin + (int)(gg / C_::kChunks);
+      chunk = (int)(gg % C_::kChunks);
+    };
+    auto issue_res_load = [&](uint32_t idx) {
+      int tile, chunk;
+      locate(idx, tile, chunk);
+      if (tile >= t_end) return;
+      const int n_tile = tile / p.m_tiles;
+      const int m_tile = tile - n_tile * p.m_tiles;
+      const uint32_t b = idx % n_res;
+      mbar_arrive_expect_tx(res_bar(grp * kMaxRes + b), C_::kChunkBytes);
+      tma_load_2d(res_base + b * C_::kChunkBytes, &tmapR, res_bar(grp * kMaxRes + b),
+                  n_tile * BN + chunk * kCW, m_tile * kBM);
+    };
+
+    uint32_t mine = 0;  // chunks processed by this group so far
+    if (has_res && leader) {
+      // fill the ring: chunks 0 .. n_res-2 (chunk i + n_res - 1 is requested when chunk i starts)
+      for (uint32_t i = 0; i + 1 < n_res; ++i) issue_res_load(i);
+    }
 
     int acc = 0;
     uint32_t acc_phase = 0;
-    uint32_t g = 0;  // global chunk counter (selects out/res buffer and res barrier phase)
-
-    auto flush_stats = [&](int n_tile) {
-      if (!p.want_stats || n_tile < 0) return;
-#pragma unroll
-      for (int j = 0; j < C_::kChunks; ++j) {
-        const int col = n_tile * BN + j * kCW + scol;
-        if (col < p.n_valid) {
-          atomicAdd(p.stats + col, acc_s1[j]);
-          atomicAdd(p.stats + p.stats_ld + col, acc_s2[j]);
-        }
-        acc_s1[j] = acc_s2[j] = 0.f;
-      }
-    };
-    auto issue_res_load = [&](int tile, int chunk, uint32_t gg) {
-      const int n_tile = tile / p.m_tiles;
-      const int m_tile = tile - n_tile * p.m_tiles;
-      const uint32_t b = gg & 1;
-      mbar_arrive_expect_tx(res_bar(b), C_::kChunkBytes);
-      tma_load_2d(sRes + b * C_::kChunkBytes, &tmapR, res_bar(b), n_tile * BN + chunk * kCW,
-                  m_tile * kBM);
-    };
-
-    const int first_tile = blockIdx.x;
-    if (has_res && leader && first_tile < p.total_tiles) issue_res_load(first_tile, 0, 0);
-
-    for (int t = first_tile; t < p.total_tiles; t += gridDim.x) {
-      const int n_tile = t / p.m_tiles;
-      const int m_tile = t - n_tile * p.m_tiles;
-      if (n_tile != cur_n_tile) {
-        flush_stats(cur_n_tile);
-        cur_n_tile = n_tile;
-        if (p.mode == DRN_EPI_BNBWD) {
-          // refresh the (scale, shift) cache for this column tile
-          named_bar_sync(1, kEpiThreads);
-          for (int i = et; i < BN; i += kEpiThreads) {
-            const int col = n_tile * BN + i;
-            sScaleShift[i] = col < p.n_valid ? p.bn_scale_shift[col] : make_float2(0.f, 0.f);
+    int tile_iter = 0;
+    for (int t = t_begin; t < t_end; ++t, ++tile_iter) {
+      const bool my_tile = C_::kChunks >= 2 || (tile_iter & 1) == grp;
+      if (my_tile) {
+        const int n_tile = t / p.m_tiles;
+        const int m_tile = t - n_tile * p.m_tiles;
+        if (n_tile != cur_n_tile) {
+          flush_stats(cur_n_tile);
+          cur_n_tile = n_tile;
+          if (p.mode == DRN_EPI_BNBWD) {
+            named_bar_sync(bar_id, kEpiThreads);
+            for (int i = et; i < BN; i += kEpiThreads) {
+              const int col = n_tile * BN + i;
+              my_ss[i] = col < p.n_valid ? p.bn_scale_shift[col] : make_float2(0.f, 0.f);
+            }
+            named_bar_sync(bar_id, kEpiThreads);
           }
-          named_bar_sync(1, kEpiThreads);
         }
-      }
-      mbar_wait(tfull_bar(acc), acc_phase, 0x40 + acc);
-      tc_fence_after();
+        mbar_wait(tfull_bar(acc), acc_phase, 0x40 + acc);
+        tc_fence_after();
 
-#pragma unroll 1
-      for (int j = 0; j < C_::kChunks; ++j, ++g) {
-        const uint32_t b = g & 1;
-        const uint32_t out_buf = sOut + b * C_::kChunkBytes;
-        const uint32_t res_buf = sRes + b * C_::kChunkBytes;
+#pragma unroll
+        for (int a = 0; a < kHalf; ++a) {
+          const int j = C_::kChunks >= 2 ? 2 * a + grp : 0;
+          const uint32_t out_buf = out_base + (mine & 1) * C_::kChunkBytes;
+          const uint32_t rb = has_res ? mine % n_res : 0;
+          const uint32_t res_buf = res_base + rb * C_::kChunkBytes;
+          // request the side input n_res-1 chunks ahead; it lands in the ring slot whose last
+          // readers finished before the closing barrier of the previous chunk
+          if (has_res && leader) issue_res_load(mine + n_res - 1);
 
-        // ---- TMEM -> registers (kCW fp32 columns of my row)
-        float v[kCW];
-        {
-          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
-                                 static_cast<uint32_t>(acc * BN + j * kCW);
-          if constexpr (kCW == 16) {
-            uint32_t r[16];
-            tmem_ld_32x16(taddr, r);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-          } else {
-#pragma unroll
-            for (int h = 0; h < kCW / 32; ++h) {
-              uint32_t r[32];
-              tmem_ld_32x32(taddr + h * 32, r);
+          // ---- TMEM -> registers (kCW fp32 columns of my row)
+          float v[kCW];
+          {
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
+                                   static_cast<uint32_t>(acc * BN + j * kCW);
+            if constexpr (kCW == 16) {
+              uint32_t r[16];
+              tmem_ld_32x16(taddr, r);
               tmem_ld_wait();
 #pragma unroll
-              for (int i = 0; i < 32; ++i) v[h * 32 + i] = __uint_as_float(r[i]);
+              for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+            } else {
+              uint32_t r[32];
+              tmem_ld_32x32(taddr, r);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
             }
           }
-        }
-        if (j == C_::kChunks - 1) {
-          // accumulator fully drained: hand the TMEM buffer back to the MMA warp
+          // every chunk's 128 threads arrive once: the buffer is free after kChunks*128 arrivals
           tc_fence_before();
           mbar_arrive(tempty_bar(acc));
-        }
 
-        // ---- out[b] must no longer be read by the store issued two chunks ago; everybody has
-        //      finished the statistics pass of the previous chunk after this barrier.
-        if (leader) tma_store_wait_read<1>();
-        named_bar_sync(1, kEpiThreads);
-
-        // prefetch the side input of the next chunk into res[b^1] (its last reader was chunk g-1)
-        if (has_res && leader) {
-          int nt = t, nj = j + 1;
-          if (nj == C_::kChunks) {
-            nj = 0;
-            nt = t + gridDim.x;
-          }
-          if (nt < p.total_tiles) issue_res_load(nt, nj, g + 1);
-        }
-
-        if (has_res) {
-          mbar_wait(res_bar(b), (g >> 1) & 1, 0x50 + b);
+          if (has_res) {
+            mbar_wait(res_bar(grp * kMaxRes + rb), (mine / n_res) & 1, 0x50 + grp * kMaxRes + rb);
+            if (p.mode == DRN_EPI_RESADD) {
 #pragma unroll
-          for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
-            const uint32_t off = swz_off(row * kRowBytes + c16 * 16, kRowBytes);
-            const uint4 rv = ld_shared_v4(res_buf + off);
-            const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
+              for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
+                const uint4 rv = ld_shared_v4(res_buf + row_off[c16]);
+                const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float y0 = bf16lo(rr[e]), y1 = bf16hi(rr[e]);
-              const int c0 = c16 * 8 + e * 2;
-              if (p.mode == DRN_EPI_RESADD) {
-                v[c0] += y0;
-                v[c0 + 1] += y1;
-              } else {  // DRN_EPI_BNBWD: keep the gradient where relu(bn(y)) was active
-                const float2 ss0 = sScaleShift[j * kCW + c0];
-                const float2 ss1 = sScaleShift[j * kCW + c0 + 1];
-                v[c0] = (fmaf(y0, ss0.x, ss0.y) > 0.f) ? v[c0] : 0.f;
-                v[c0 + 1] = (fmaf(y1, ss1.x, ss1.y) > 0.f) ? v[c0 + 1] : 0.f;
+                for (int e = 0; e < 4; ++e) {
+                  v[c16 * 8 + e * 2] += bf16lo(rr[e]);
+                  v[c16 * 8 + e * 2 + 1] += bf16hi(rr[e]);
+                }
+              }
+            } else {  // DRN_EPI_BNBWD: keep the gradient where relu(bn(y)) was active
+#pragma unroll
+              for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
+                const uint4 rv = ld_shared_v4(res_buf + row_off[c16]);
+                const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const int c0 = c16 * 8 + e * 2;
+                  const float2 ss0 = my_ss[j * kCW + c0];
+                  const float2 ss1 = my_ss[j * kCW + c0 + 1];
+                  v[c0] = (fmaf(bf16lo(rr[e]), ss0.x, ss0.y) > 0.f) ? v[c0] : 0.f;
+                  v[c0 + 1] = (fmaf(bf16hi(rr[e]), ss1.x, ss1.y) > 0.f) ? v[c0 + 1] : 0.f;
+                }
               }
             }
           }
-        }
 
-        // ---- registers -> swizzled smem (bf16)
+          // ---- registers -> swizzled smem (bf16); out_buf is free (closing barrier, last chunk)
 #pragma unroll
-        for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
-          const uint32_t off = swz_off(row * kRowBytes + c16 * 16, kRowBytes);
-          st_shared_v4(out_buf + off, pack_bf16x2(v[c16 * 8 + 0], v[c16 * 8 + 1]),
-                       pack_bf16x2(v[c16 * 8 + 2], v[c16 * 8 + 3]),
-                       pack_bf16x2(v[c16 * 8 + 4], v[c16 * 8 + 5]),
-                       pack_bf16x2(v[c16 * 8 + 6], v[c16 * 8 + 7]));
-        }
-        fence_proxy_async_smem();
-        named_bar_sync(1, kEpiThreads);
-        if (leader) {
-          tma_store_2d(&tmapC, out_buf, n_tile * BN + j * kCW, m_tile * kBM);
-          tma_store_commit();
-        }
+          for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
+            st_shared_v4(out_buf + row_off[c16], pack_bf16x2(v[c16 * 8 + 0], v[c16 * 8 + 1]),
+                         pack_bf16x2(v[c16 * 8 + 2], v[c16 * 8 + 3]),
+                         pack_bf16x2(v[c16 * 8 + 4], v[c16 * 8 + 5]),
+                         pack_bf16x2(v[c16 * 8 + 6], v[c16 * 8 + 7]));
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(bar_id, kEpiThreads);
+          if (leader) {
+            tma_store_2d(&tmapC, out_buf, n_tile * BN + j * kCW, m_tile * kBM);
+            tma_store_commit();
+          }
 
-        // ---- per-channel statistics of what was just stored (bf16-rounded values)
-        if (p.want_stats) {
-          float s1 = 0.f, s2 = 0.f;
-          const uint32_t cbyte = scol * 2;
-#pragma unroll 8
-          for (int rr = 0; rr < kRowsPerThread; ++rr) {
-            const uint32_t off = swz_off((srow0 + rr) * kRowBytes + cbyte, kRowBytes);
-            const float o = __uint_as_float(ld_shared_u16(out_buf + off) << 16);
-            s1 += o;
+          // ---- per-channel statistics of what was just stored (bf16-rounded values)
+          if (p.want_stats) {
             if (p.mode == DRN_EPI_BNBWD) {
-              const float y = __uint_as_float(ld_shared_u16(res_buf + off) << 16);
-              s2 = fmaf(o, y, s2);
+#pragma unroll
+              for (int i = 0; i < kNcg; ++i) {
+                const uint4 ov = ld_shared_v4(out_buf + st_off[i]);
+                const uint4 yv = ld_shared_v4(res_buf + st_off[i]);
+                const uint32_t oo[4] = {ov.x, ov.y, ov.z, ov.w};
+                const uint32_t yy[4] = {yv.x, yv.y, yv.z, yv.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float o0 = bf16lo(oo[e]), o1 = bf16hi(oo[e]);
+                  acc1[a][2 * e] += o0;
+                  acc1[a][2 * e + 1] += o1;
+                  acc2[a][2 * e] = fmaf(o0, bf16lo(yy[e]), acc2[a][2 * e]);
+                  acc2[a][2 * e + 1] = fmaf(o1, bf16hi(yy[e]), acc2[a][2 * e + 1]);
+                }
+              }
             } else {
-              s2 = fmaf(o, o, s2);
+#pragma unroll
+              for (int i = 0; i < kNcg; ++i) {
+                const uint4 ov = ld_shared_v4(out_buf + st_off[i]);
+                const uint32_t oo[4] = {ov.x, ov.y, ov.z, ov.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float o0 = bf16lo(oo[e]), o1 = bf16hi(oo[e]);
+                  acc1[a][2 * e] += o0;
+                  acc1[a][2 * e + 1] += o1;
+                  acc2[a][2 * e] = fmaf(o0, o0, acc2[a][2 * e]);
+                  acc2[a][2 * e + 1] = fmaf(o1, o1, acc2[a][2 * e + 1]);
+                }
+              }
             }
           }
-          acc_s1[j] += s1;
-          acc_s2[j] += s2;
+          // The other out buffer (next chunk's) was last read by the store issued one chunk ago:
+          // wait for everything but the newest store, then let the whole group move on.
+          if (leader) tma_store_wait_read<1>();
+          named_bar_sync(bar_id, kEpiThreads);
+          ++mine;
         }
       }
       acc ^= 1;
@@ -417,6 +498,10 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   p.pad_h = d.pad_lo;
   p.pad_w = d.pad_lo;
   p.mode = mode;
+  p.n_res = mode == DRN_EPI_PLAIN ? 0 : (BN >= 256 ? 3 : 4);
+  p.n_stages = C_::stages_for(p.n_res);
+  if (p.n_stages < 2) return fail("conv_igemm: shared memory plan does not fit (KC=%d BN=%d)", KC, BN);
+  const int smem_bytes = C_::smem_for(p.n_res, p.n_stages);
   p.want_stats = stats != nullptr;
   p.n_valid = d.K;
   p.stats_ld = stats_ld;
@@ -442,12 +527,11 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   static bool attr_set = false;
   if (!attr_set) {
     DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        C_::kSmemBytes));
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
     attr_set = true;
   }
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
-  conv_igemm_kernel<KC, BN><<<grid, kNumThreads, C_::kSmemBytes, stream>>>(tA, tB, tC, tR, p);
+  conv_igemm_kernel<KC, BN><<<grid, kNumThreads, smem_bytes, stream>>>(tA, tB, tC, tR, p);
   DRN_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -485,7 +569,10 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
   DRN_REQUIRE(stats == nullptr || stats_ld >= d.K, "conv_igemm: stats_ld < K");
   int bn = force_bn;
   if (bn == 0) {
-    if (d.K % 256 == 0) bn = 256;
+    // 256-wide tiles leave room for only two pipeline stages next to the side-input ring: keep
+    // them for shallow reductions, use 128 when the K loop is long
+    const bool deep_k = d.R * d.S * d.C > 256;
+    if (d.K % 256 == 0 && !(mode != DRN_EPI_PLAIN && deep_k)) bn = 256;
     else if (d.K % 128 == 0) bn = 128;
     else if (d.K % 64 == 0) bn = 64;
     else if (d.K % 32 == 0) bn = 32;
