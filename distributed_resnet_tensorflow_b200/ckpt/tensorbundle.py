@@ -346,10 +346,10 @@ def write_bundle(prefix: str, tensors: Dict[str, np.ndarray]) -> None:
             arr = np.asarray(tensors[name])
             if arr.dtype not in _NP_TO_DT:
                 raise TypeError(f"{name}: unsupported dtype {arr.dtype}")
-            arr = np.ascontiguousarray(arr.astype(arr.dtype.newbyteorder("<"), copy=False))
-            raw = arr.tobytes()
+            shape = arr.shape  # np.ascontiguousarray would promote 0-d arrays to 1-d
+            raw = arr.astype(arr.dtype.newbyteorder("<"), copy=False).tobytes(order="C")
             f.write(raw)
-            items.append((name.encode(), encode_entry(_NP_TO_DT[arr.dtype], arr.shape, 0, offset,
+            items.append((name.encode(), encode_entry(_NP_TO_DT[arr.dtype], shape, 0, offset,
                                                       len(raw), masked_crc32c(raw))))
             offset += len(raw)
     index_tmp = prefix + ".index.tmp"

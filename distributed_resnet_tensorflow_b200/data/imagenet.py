@@ -1,0 +1,107 @@
+"""ImageNet TFRecord input (reference resnet_imagenet_main.py:103-183).
+
+Pipeline per replica (unsharded, as in the reference): shuffle the shard list (buffer 1024) ->
+read records -> parse tf.Example (``image/encoded``, ``image/class/label``) -> decode JPEG (PIL,
+worker threads standing in for tf.data's ``num_threads=5``) -> VGG resize + crop on the host ->
+shuffle buffer of 1500 examples -> batches of uint8 224x224x3 crops + labels + flip flags.
+Scaling, flipping, mean subtraction and the space-to-depth layout run on the device.
+"""
+from __future__ import annotations
+
+import io
+import os
+from concurrent.futures import ThreadPoolExecutor
+from typing import Iterator, List, Optional, Tuple
+
+import numpy as np
+
+from . import preprocess
+from .tfrecord import parse_example, read_tfrecords
+
+FILE_SHUFFLE_BUFFER = 1024
+SHUFFLE_BUFFER = 1500
+NUM_IMAGES = {"train": 1281167, "validation": 50000}
+
+
+def filenames(is_training: bool, data_dir: str) -> List[str]:
+    if is_training:
+        return [os.path.join(data_dir, "train-%05d-of-01024" % i) for i in range(1024)]
+    return [os.path.join(data_dir, "validation-%05d-of-00128" % i) for i in range(128)]
+
+
+def decode_image(encoded: bytes) -> np.ndarray:
+    from PIL import Image
+    img = Image.open(io.BytesIO(encoded)).convert("RGB")
+    return np.asarray(img, dtype=np.uint8)
+
+
+def parse_record(payload: bytes) -> Tuple[bytes, int]:
+    ex = parse_example(payload)
+    enc = ex.get("image/encoded", [b""])
+    lab = ex.get("image/class/label", [-1])
+    return (enc[0] if enc else b""), int(lab[0] if lab else -1)
+
+
+class ImageNetBatches:
+    def __init__(self, data_dir: str, batch_size: int, training: bool, num_epochs: Optional[int] = None,
+                 seed: int = 0, num_threads: int = 5, files: Optional[List[str]] = None):
+        self.files = files if files is not None else [f for f in filenames(training, data_dir) if os.path.exists(f)]
+        if not self.files:
+            raise FileNotFoundError(f"no ImageNet TFRecord shards under {data_dir!r}")
+        self.B, self.training, self.num_epochs = batch_size, training, num_epochs
+        self.rng = np.random.default_rng(seed)
+        self.pool = ThreadPoolExecutor(max_workers=max(1, num_threads))
+
+    def _examples(self) -> Iterator[Tuple[np.ndarray, int, int]]:
+        epoch = 0
+        while self.num_epochs is None or epoch < self.num_epochs:
+            files = list(self.files)
+            if self.training:
+                self.rng.shuffle(files)
+
+            def work(payload, seed):
+                enc, lab = parse_record(payload)
+                img = decode_image(enc)
+                crop, flip = preprocess.vgg_resize_crop_u8(img, self.training, 224,
+                                                           np.random.default_rng(seed))
+                return crop, lab, flip
+
+            pending = []
+            for f in files:
+                for payload in read_tfrecords(f):
+                    pending.append(self.pool.submit(work, payload, int(self.rng.integers(0, 2 ** 31))))
+                    if len(pending) >= 4 * self.B:
+                        yield pending.pop(0).result()
+            for p in pending:
+                yield p.result()
+            epoch += 1
+
+    def __iter__(self) -> Iterator[Tuple[np.ndarray, np.ndarray, np.ndarray]]:
+        """Yields (images uint8 [B, 224*224*3], labels int32 [B], crop int32 [B,3] = (0,0,flip))."""
+        buf: List[Tuple[np.ndarray, int, int]] = []
+        out: List[Tuple[np.ndarray, int, int]] = []
+        cap = SHUFFLE_BUFFER if self.training else 1
+
+        def emit():
+            imgs = np.stack([o[0].reshape(-1) for o in out])
+            labs = np.asarray([o[1] for o in out], np.int32)
+            crop = np.asarray([[0, 0, o[2]] for o in out], np.int32)
+            out.clear()
+            return imgs, labs, crop
+
+        for ex in self._examples():
+            buf.append(ex)
+            if len(buf) >= cap:
+                i = int(self.rng.integers(0, len(buf))) if self.training else 0
+                buf[i], buf[-1] = buf[-1], buf[i]
+                out.append(buf.pop())
+                if len(out) == self.B:
+                    yield emit()
+        if self.training:
+            self.rng.shuffle(buf)
+        for ex in buf:
+            out.append(ex)
+            if len(out) == self.B:
+                yield emit()
+        if out:
+            yield emit()
