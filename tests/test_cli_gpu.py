@@ -1,0 +1,51 @@
+"""Command-line entry points on one GPU with the native backend: train -> checkpoint -> separate
+eval process -> resume; and cross-backend checkpoint compatibility."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(args, timeout=900):
+    res = subprocess.run([sys.executable] + args, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
+    assert res.returncode == 0, (res.stdout + res.stderr)[-4000:]
+    return res.stdout + res.stderr
+
+
+def test_cifar_train_eval_resume_native(tmp_path):
+    from distributed_resnet_tensorflow_b200.ckpt.saver import Saver, latest_checkpoint
+    root = str(tmp_path / "ckpt")
+    common = ["--resnet_size=14", "--batch_size=64", "--num_gpus=1", f"--log_root={root}",
+              f"--eval_dir={tmp_path / 'ev'}", "--log_every=20", "--base_lr=0.05"]
+    out = _run([os.path.join(ROOT, "resnet_cifar_main.py"), "--train_steps=80"] + common)
+    assert "backend=native" in out and "step = 80" in out
+    train_prec = float(out.split("step = 80,")[1].split("precision = ")[1].split(",")[0])
+    assert train_prec > 0.5, out[-800:]     # learnable synthetic data: the native path really trains
+    v = Saver.restore(latest_checkpoint(root))
+    assert int(v["global_step"]) == 80 and len(v) == 2 * 44 + 2 * 13 + 1
+    ev = _run([os.path.join(ROOT, "resnet_cifar_eval.py"), "--resnet_size=14", "--num_gpus=1", f"--log_root={root}",
+               f"--eval_dir={tmp_path / 'ev2'}", "--eval_once=True", "--eval_batch_count=5"])
+    assert "best precision" in ev
+    prec = float(ev.split("precision:")[1].split(",")[0])
+    loss = float(ev.split("loss:")[1].split(",")[0])
+    # (after 80 steps the 0.997-decay moving statistics are far from converged, so inference-mode
+    #  precision is low by construction - exactly as it would be in the reference)
+    # the same checkpoint evaluated by the PyTorch backend agrees (TF-name / layout map is consistent)
+    ev_t = _run([os.path.join(ROOT, "resnet_cifar_eval.py"), "--resnet_size=14", "--num_gpus=1", "--backend=torch",
+                 "--dtype=fp32", f"--log_root={root}", "--eval_once=True", "--eval_batch_count=5"])
+    prec_t = float(ev_t.split("precision:")[1].split(",")[0])
+    loss_t = float(ev_t.split("loss:")[1].split(",")[0])
+    assert abs(prec - prec_t) < 0.05 and abs(loss - loss_t) < 0.05 * max(1.0, loss_t), (prec, prec_t, loss, loss_t)
+    out2 = _run([os.path.join(ROOT, "resnet_cifar_main.py"), "--train_steps=100"] + common)
+    assert "restored" in out2 and "step = 100" in out2
+
+
+def test_imagenet_main_serial_native(tmp_path):
+    out = _run([os.path.join(ROOT, "resnet_imagenet_main.py"), "--resnet_size=18", "--batch_size=16", "--num_gpus=1",
+                "--train_steps=12", "--log_every=4", f"--log_root={tmp_path / 'ckpt'}", f"--train_dir={tmp_path / 'tr'}"])
+    assert "backend=native" in out and "step = 12" in out
