@@ -587,3 +587,46 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
     default: return dispatch_bn<64>(bn, d, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, st);
   }
 }
+
+// ------------------------------------------------------------------------------------------------
+// Data gradient as a first-class entry point: callers describe the FORWARD convolution and get dx;
+// the geometry of the equivalent stride-1 convolution over (zero-inserted) dy is derived here.
+// ------------------------------------------------------------------------------------------------
+namespace drn {
+int dgrad_geometry(const drn_conv_desc& d, drn_conv_desc* g) {
+  const int U = (d.P - 1) * d.stride + 1, V = (d.Q - 1) * d.stride + 1;
+  const int pad_lo = d.R - 1 - d.pad_lo;
+  const int pad_hi_h = d.H - U + d.pad_lo, pad_hi_w = d.W - V + d.pad_lo;
+  DRN_REQUIRE(d.R == d.S && pad_hi_h == pad_hi_w, "conv_dgrad: square filters / symmetric geometry only");
+  DRN_REQUIRE(pad_lo >= 0 && pad_hi_h >= 0, "conv_dgrad: padding larger than the filter is not supported");
+  g->N = d.N; g->H = U; g->W = V; g->C = d.K; g->K = d.C; g->R = d.R; g->S = d.S; g->stride = 1;
+  g->pad_lo = pad_lo; g->pad_hi = pad_hi_h; g->P = d.H; g->Q = d.W;
+  return 0;
+}
+}  // namespace drn
+
+extern "C" long long drn_conv_dgrad_scratch_bytes(const drn_conv_desc* desc) {
+  if (desc->stride == 1) return 0;
+  const long long U = (long long)(desc->P - 1) * desc->stride + 1, V = (long long)(desc->Q - 1) * desc->stride + 1;
+  return 2LL * desc->N * U * V * desc->K;
+}
+
+extern "C" int drn_conv_dgrad(const drn_conv_desc* desc, const void* dy, const void* w_dgrad, void* dx,
+                              const void* side, float* stats, int stats_ld, const void* bn_scale_shift,
+                              int mode, void* scratch, long long scratch_bytes, void* stream) {
+  using namespace drn;
+  drn_conv_desc g;
+  if (int e = dgrad_geometry(*desc, &g)) return e;
+  const void* src = dy;
+  if (desc->stride > 1) {
+    const long long need = drn_conv_dgrad_scratch_bytes(desc);
+    DRN_REQUIRE(scratch != nullptr && scratch_bytes >= need,
+                "conv_dgrad: stride %d needs %lld bytes of scratch (got %lld)", desc->stride, need,
+                scratch_bytes);
+    if (int e = drn_upsample_zero(dy, scratch, desc->N, desc->P, desc->Q, g.H, g.W, desc->K,
+                                  desc->stride, stream))
+      return e;
+    src = scratch;
+  }
+  return drn_conv_igemm(&g, src, w_dgrad, dx, side, stats, stats_ld, bn_scale_shift, mode, 0, stream);
+}

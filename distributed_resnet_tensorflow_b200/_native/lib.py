@@ -39,6 +39,8 @@ _SIGNATURES = {
     "drn_num_sms": (_i, []),
     "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
+    "drn_conv_dgrad_scratch_bytes": (_ll, [ctypes.POINTER(ConvDesc)]),
+    "drn_conv_dgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _ll, _vp]),
     "drn_bn_finalize": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _i, _vp]),
     "drn_bn_inference_params": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _i, _vp]),
     "drn_bn_apply": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp]),
@@ -126,6 +128,12 @@ def launch_count() -> int:
     """Number of kernel-launching C calls made through ``call`` since the last reset (every
     ``drn_*`` launcher enqueues exactly one kernel of this library)."""
     return _launch_count
+
+
+def add_launches(n: int) -> None:
+    """For entry points that enqueue more than one kernel (e.g. strided drn_conv_dgrad)."""
+    global _launch_count
+    _launch_count += n
 
 
 def call(name: str, *args) -> None:

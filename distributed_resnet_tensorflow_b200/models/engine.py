@@ -423,15 +423,13 @@ class NativeResNet:
         _nl.call("drn_bn_apply", _p(y), _p(bn.ss), 0, _p(out), M, bn.C, 1, self._st())
 
     def _dgrad(self, conv: _Conv, dy, out, side=None, stats=None, ss=None, mode=EPI_PLAIN):
-        """Data gradient of ``conv`` given dy; writes [B, H, W, Cin] into ``out``."""
-        src = dy
-        if conv.g.stride > 1:
-            if conv.g.R == 1:
-                raise AssertionError("1x1 strided dgrad is handled by the caller (compact form)")
-            _nl.call("drn_upsample_zero", _p(dy), _p(conv.up), conv.g.N, conv.g.P, conv.g.Q,
-                     conv.dg.H, conv.dg.W, conv.g.K, conv.g.stride, self._st())
-            src = conv.up
-        self._conv(conv.dg_desc, src, conv.wd, out, side=side, stats=stats, ss=ss, mode=mode)
+        """Data gradient of ``conv`` given dy; writes [B, H, W, Cin] into ``out``. Strided
+        convolutions use the per-layer zero-insertion buffer ``conv.up`` as scratch."""
+        _nl.call("drn_conv_dgrad", ctypes.byref(conv.desc), _p(dy), _p(conv.wd), _p(out), _p(side),
+                 _p(stats), stats.stride(0) if stats is not None else 0, _p(ss), mode, _p(conv.up),
+                 conv.up.numel() * 2 if conv.up is not None else 0, self._st())
+        if conv.up is not None:
+            _nl.add_launches(1)   # zero-insertion kernel + implicit GEMM
 
     # ---- forward ------------------------------------------------------------------------------
     def forward(self, training: bool = True) -> None:

@@ -100,3 +100,21 @@ def conv_wgrad(x, dy, g: ConvGeom, dw=None, split_k: int = 0):
     d = g.desc()
     _nl.call("drn_conv_wgrad", ctypes.byref(d), _ptr(x), _ptr(dy), _ptr(dw), split_k, _stream())
     return dw
+
+
+def conv_dgrad(dy, w_dgrad, g: ConvGeom, out=None, side=None, stats=None, bn_scale_shift=None,
+               mode: int = EPI_PLAIN, scratch=None):
+    """dx[N,H,W,C] for the forward geometry ``g`` (filters prepared by drn_weight_prep_dgrad).
+    ``scratch`` (bf16) is required for stride > 1; allocated here when missing."""
+    d = g.desc()
+    lib = _nl.load()
+    need = lib.drn_conv_dgrad_scratch_bytes(ctypes.byref(d))
+    if need and scratch is None:
+        scratch = torch.empty(need // 2, dtype=torch.bfloat16, device=dy.device)
+    if out is None:
+        out = torch.empty((g.N, g.H, g.W, g.C), dtype=torch.bfloat16, device=dy.device)
+    stats_ld = stats.stride(0) if stats is not None else 0
+    _nl.call("drn_conv_dgrad", ctypes.byref(d), _ptr(dy), _ptr(w_dgrad), _ptr(out), _ptr(side), _ptr(stats),
+             stats_ld, _ptr(bn_scale_shift), mode, _ptr(scratch), scratch.numel() * 2 if scratch is not None else 0,
+             _stream())
+    return out

@@ -58,6 +58,16 @@ int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const void* w, void
                    const void* side, float* stats, int stats_ld, const void* bn_scale_shift,
                    int mode, int force_bn, void* stream);
 
+/* Data gradient (K2) of the convolution described by `desc` (FORWARD geometry):
+ *   dx[N,H,W,C] = sum_{k,r,s} dy[N,P,Q,K] (x) w,  given w_dgrad = drn_weight_prep_dgrad(w).
+ * Runs the implicit-GEMM kernel above on the equivalent stride-1 problem; for stride > 1 dy is first
+ * zero-inserted into `scratch` (bf16 [N,(P-1)s+1,(Q-1)s+1,K]; drn_conv_dgrad_scratch_bytes(desc),
+ * 0 for stride 1). side / stats / bn_scale_shift / mode as in drn_conv_igemm, shaped like dx. */
+long long drn_conv_dgrad_scratch_bytes(const drn_conv_desc* desc);
+int drn_conv_dgrad(const drn_conv_desc* desc, const void* dy, const void* w_dgrad, void* dx,
+                   const void* side, float* stats, int stats_ld, const void* bn_scale_shift, int mode,
+                   void* scratch, long long scratch_bytes, void* stream);
+
 /* Filter gradient (K3): dw[K][R][S][C] (fp32) += sum over pixels of dy[.,k] * x[. + (r,s), c].
  *   x  [N,H,W,C] bf16   dy [N,P,Q,K] bf16   dw fp32, ACCUMULATED with atomics (zero it first).
  *   split_k: 0 = choose automatically. */

@@ -63,6 +63,9 @@ def test_dgrad_via_flipped_filters(ks, st):
         nl.call("drn_upsample_zero", _p(dy), _p(src), N, g.P, g.Q, dg.H, dg.W, K, st, _st())
     dx = conv_fprop(src, wd, dg)
     assert tuple(dx.shape) == (N, H, H, C)
+    from distributed_resnet_tensorflow_b200.ops.conv import conv_dgrad
+    dx2 = conv_dgrad(dy, wd, g)            # the C entry point that derives the geometry itself
+    assert torch.equal(dx, dx2)
     xz = torch.zeros((N, C, H + g.pad_lo + g.pad_hi, H + g.pad_lo + g.pad_hi), device="cuda")
     ref = torch.nn.grad.conv2d_input(xz.shape, w.float().permute(0, 3, 1, 2), dy.float().permute(0, 3, 1, 2), stride=st)
     ref = ref[:, :, g.pad_lo:g.pad_lo + H, g.pad_lo:g.pad_lo + H].permute(0, 2, 3, 1)
