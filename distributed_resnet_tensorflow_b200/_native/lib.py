@@ -41,6 +41,7 @@ _SIGNATURES = {
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
     "drn_conv_dgrad_scratch_bytes": (_ll, [ctypes.POINTER(ConvDesc)]),
     "drn_conv_dgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _ll, _vp]),
+    "drn_conv_dgrad_static": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp]),
     "drn_bn_finalize": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _i, _vp]),
     "drn_bn_inference_params": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _i, _vp]),
     "drn_bn_apply": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp]),

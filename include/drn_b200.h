@@ -68,6 +68,19 @@ int drn_conv_dgrad(const drn_conv_desc* desc, const void* dy, const void* w_dgra
                    const void* side, float* stats, int stats_ld, const void* bn_scale_shift, int mode,
                    void* scratch, long long scratch_bytes, void* stream);
 
+/* Same operation as drn_conv_dgrad for callers that cannot allocate device memory when they call -
+ * e.g. a process that gave the whole GPU to its own memory pool, or a latency-critical loop where
+ * cudaMalloc/cudaFree (which synchronise the device) are off limits.  The zero-insertion scratch
+ * lives in a fixed DRN_DGRAD_STATIC_SCRATCH_BYTES array inside the library (reserved on every GPU
+ * that loads it); larger problems are refused with an error.  The first call on a device resolves
+ * the array's device address - make it at start-up, before any stream capture.  All calls share
+ * the array: every call rewrites what it uses, so nothing has to be cleared, but calls that can
+ * overlap on the GPU race with each other.  Allocates nothing.  No counterpart in the reference. */
+#define DRN_DGRAD_STATIC_SCRATCH_BYTES (16u << 20)
+int drn_conv_dgrad_static(const drn_conv_desc* desc, const void* dy, const void* w_dgrad, void* dx,
+                          const void* side, float* stats, int stats_ld, const void* bn_scale_shift,
+                          int mode, void* stream);
+
 /* Filter gradient (K3): dw[K][R][S][C] (fp32) += sum over pixels of dy[.,k] * x[. + (r,s), c].
  *   x  [N,H,W,C] bf16   dy [N,P,Q,K] bf16   dw fp32, ACCUMULATED with atomics (zero it first).
  *   split_k: 0 = choose automatically. */
