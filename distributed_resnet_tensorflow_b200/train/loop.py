@@ -205,6 +205,10 @@ def train(cfg: Config) -> Dict[str, float]:
     be.import_variables(variables)
     if ctx.distributed:
         _assert_replicas_agree(variables, ctx, device)
+        if isinstance(be, NativeBackend) and be.comm is not None:
+            # BroadcastGlobalVariablesHook(0) (resnet_cifar_main_horovod.py:316): chief's master,
+            # momentum and BN statistics overwrite every replica's through the NVLink broadcast kernel
+            be.comm.broadcast_arena(be.trainer.engine, root=0)
 
     if ctx.role == "ps":
         while be.ps_serve_step():

@@ -52,6 +52,25 @@ def main():
         if rank == 0:
             print(f"allreduce multicast={use_mc} provider={red.grad_buf.provider} maxerr={err:.2e}", flush=True)
 
+    # ---------------- broadcast of the chief's variables (C3) ------------------------------------
+    from distributed_resnet_tensorflow_b200.models.init import init_variables as _iv
+    from distributed_resnet_tensorflow_b200.models.spec import build_spec as _bs
+    from distributed_resnet_tensorflow_b200.train.native import NativeTrainer as _NT
+    _spec = _bs("cifar10", 8)
+    _comm = AllreduceReducer(rank, world, dev, provider=provider)
+    _tr = _NT(_spec, 8, device=dev, comm=_comm, use_graph=False)
+    _tr.import_variables(_iv(_spec, seed=100 + rank))         # every rank starts DIFFERENT
+    _comm.broadcast_arena(_tr.engine, root=0)
+    want_w = _tr.engine.master.clone(); dist.broadcast(want_w, 0)
+    assert torch.equal(_tr.engine.master, want_w), "broadcast_arena: master differs from the chief's"
+    chief = _iv(_spec, seed=100)
+    got = _tr.export_variables()
+    assert np.array_equal(got["conv2d_3/kernel"], chief["conv2d_3/kernel"])
+    assert torch.equal(_tr.engine.shadow.float(), _tr.engine.master.bfloat16().float())
+    if rank == 0:
+        print("bcast: chief variables on all ranks ok", flush=True)
+    del _tr, _comm
+
     # ---------------- end-to-end: 2-replica step == mean-gradient step --------------------------
     from distributed_resnet_tensorflow_b200.models.init import init_variables
     from distributed_resnet_tensorflow_b200.models.spec import build_spec

@@ -140,3 +140,21 @@ def test_imagenet_batches_from_shards(tmp_path):
     batches = list(ImageNetBatches(str(tmp_path), 4, False, num_epochs=1, files=[f]))
     assert [b[0].shape for b in batches] == [(4, 224 * 224 * 3), (2, 224 * 224 * 3)]
     assert list(batches[0][1]) == [1, 2, 3, 4] and batches[0][2].shape == (4, 3)
+
+
+def test_legacy_build_input_and_vgg_module(tmp_path):
+    from distributed_resnet_tensorflow_b200.data import cifar_input, vgg_preprocessing
+    imgs, labs = synthetic_cifar(40, 100, seed=3)
+    p = str(tmp_path / "test_batch.bin")
+    cifar.write_records(p, imgs, labs % 100, "cifar100")
+    batches = list(cifar_input.build_input("cifar100", str(tmp_path / "test_batch*"), 10, "eval", num_epochs=1))
+    assert len(batches) == 4 and batches[0][0].shape == (10, 32, 32, 3) and batches[0][1].shape == (10, 100)
+    assert np.array_equal(batches[0][1].argmax(1), (labs % 100)[:10])
+    tr = next(iter(cifar_input.build_input("cifar100", p, 8, "train")))
+    assert tr[0].shape == (8, 32, 32, 3) and abs(tr[0][0].mean()) < 1e-3
+    with pytest.raises(ValueError):
+        next(iter(cifar_input.build_input("mnist", p, 8, "train")))
+    img = np.random.default_rng(0).random((300, 280, 3)).astype(np.float32)
+    out = vgg_preprocessing.preprocess_image(img, 224, 224, is_training=False)
+    assert out.shape == (224, 224, 3) and np.allclose(out, preprocess.vgg_preprocess(img, False))
+    assert vgg_preprocessing.preprocess_image(img, 224, 224, True, rng=np.random.default_rng(1)).shape == (224, 224, 3)

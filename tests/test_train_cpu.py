@@ -97,3 +97,14 @@ def test_profile_report_lists_params_and_flops():
     from distributed_resnet_tensorflow_b200.train.loop import profile_report
     rep = profile_report(imagenet_resnet(50), 128)
     assert "25551401" in rep and "8.178 GFLOP/image" in rep
+
+
+def test_resnet_single_train_eval_mode(tmp_path):
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, os.path.join(root, "resnet_single.py"), "--mode=train_eval", "--resnet_size=8",
+                          "--batch_size=8", "--train_steps=6", "--eval_every=3", "--eval_batch_count=1",
+                          f"--log_root={tmp_path / 'ckpt'}", "--log_every=3"], capture_output=True, text=True, timeout=600)
+    out = res.stdout + res.stderr
+    assert res.returncode == 0, out[-3000:]
+    assert "total trainable parameters" in out and out.count("best precision") == 2 and "step = 6" in out
