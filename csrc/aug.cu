@@ -93,7 +93,7 @@ __global__ void cifar_augment_kernel(const uint8_t* __restrict__ records, int re
 __global__ void imagenet_prep_kernel(const uint8_t* __restrict__ src, long long image_stride,
                                      int src_h, int src_w, const int* __restrict__ crop_yx_flip,
                                      __nv_bfloat16* __restrict__ out, int B, int crop, float mean_r,
-                                     float mean_g, float mean_b) {
+                                     float mean_g, float mean_b, int out_pitch, int out_xoff) {
   const int half = crop / 2;
   const long long total = (long long)B * half * half;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -133,7 +133,8 @@ __global__ void imagenet_prep_kernel(const uint8_t* __restrict__ src, long long 
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) packed[k] = pack_bf16x2(vals[2 * k], vals[2 * k + 1]);
-    uint4* dst = reinterpret_cast<uint4*>(out + i * 16);
+    // rows of the output may be wider than crop/2 pixels (zero borders owned by the caller)
+    uint4* dst = reinterpret_cast<uint4*>(out + (((long long)b * half + ii) * out_pitch + j + out_xoff) * 16);
     dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
     dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
   }
@@ -179,15 +180,17 @@ extern "C" int drn_cifar_augment(const void* records, int record_stride, int ima
 
 extern "C" int drn_imagenet_prep(const void* src, long long image_stride, int src_h, int src_w,
                                  const int* crop_yx_flip, void* out, int B, int crop, float mean_r,
-                                 float mean_g, float mean_b, void* stream) {
+                                 float mean_g, float mean_b, int out_pitch, int out_xoff, void* stream) {
   DRN_REQUIRE(crop % 2 == 0, "imagenet_prep: crop size must be even");
+  if (out_pitch <= 0) out_pitch = crop / 2;
+  DRN_REQUIRE(out_xoff >= 0 && out_xoff + crop / 2 <= out_pitch, "imagenet_prep: bad output pitch/offset");
   const long long total = (long long)B * (crop / 2) * (crop / 2);
   long long blocks = (total + 255) / 256;
   const long long cap = (long long)num_sms() * 8;
   if (blocks > cap) blocks = cap;
   imagenet_prep_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
       (const uint8_t*)src, image_stride, src_h, src_w, crop_yx_flip, (__nv_bfloat16*)out, B, crop,
-      mean_r, mean_g, mean_b);
+      mean_r, mean_g, mean_b, out_pitch, out_xoff);
   DRN_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -495,8 +495,12 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   p.Q = Q;
   p.stride_h = d.stride;
   p.stride_w = d.stride;
+  const ConvView* view = current_view();
+  const int pad_w_lo = view ? view->pad_w_lo : d.pad_lo, pad_w_hi = view ? view->pad_w_hi : d.pad_hi;
+  long long vstr[3] = {0, 0, 0};
+  if (view) { vstr[0] = view->stride_w; vstr[1] = view->stride_h; vstr[2] = view->stride_n; }
   p.pad_h = d.pad_lo;
-  p.pad_w = d.pad_lo;
+  p.pad_w = pad_w_lo;
   p.mode = mode;
   p.n_res = mode == DRN_EPI_PLAIN ? 0 : (BN >= 256 ? 3 : 4);
   p.n_stages = C_::stages_for(p.n_res);
@@ -509,9 +513,9 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   p.bn_scale_shift = reinterpret_cast<const float2*>(bn_scale_shift);
 
   CUtensorMap tA, tB, tC, tR;
-  if (int e = tmap_im2col_nhwc(&tA, x, d.N, d.H, d.W, d.C, -d.pad_lo, -d.pad_lo,
-                               d.pad_hi - (d.R - 1), d.pad_hi - (d.S - 1), d.stride, d.stride, KC,
-                               kBM, KC * 2))
+  if (int e = tmap_im2col_nhwc(&tA, x, d.N, d.H, d.W, d.C, -d.pad_lo, -pad_w_lo,
+                               d.pad_hi - (d.R - 1), pad_w_hi - (d.S - 1), d.stride, d.stride, KC,
+                               kBM, KC * 2, view ? vstr : nullptr))
     return e;
   if (int e = tmap_tiled_2d(&tB, w, 2, d.K, (uint64_t)d.R * d.S * d.C, (uint64_t)d.R * d.S * d.C,
                             BN, KC, KC * 2))
@@ -629,4 +633,18 @@ extern "C" int drn_conv_dgrad(const drn_conv_desc* desc, const void* dy, const v
     src = scratch;
   }
   return drn_conv_igemm(&g, src, w_dgrad, dx, side, stats, stats_ld, bn_scale_shift, mode, 0, stream);
+}
+
+// Convolution over a strided / overlapping VIEW of the input (strides in elements, separate W
+// padding). Used for the space-to-depth ImageNet stem: viewing the zero-bordered [B,112,116,16]
+// tensor as [B,112,112,64] with a W stride of 16 elements turns the four horizontal taps of the
+// 4x4 filter into one 64-channel (128-byte) TMA row, i.e. a 4x1 convolution with K = 4 x 64.
+extern "C" int drn_conv_igemm_view(const drn_conv_desc* desc, const drn_conv_view* view, const void* x,
+                                   const void* w, void* y, const void* side, float* stats, int stats_ld,
+                                   const void* bn_scale_shift, int mode, int force_bn, void* stream) {
+  drn::ConvView v{view->stride_w, view->stride_h, view->stride_n, view->pad_w_lo, view->pad_w_hi};
+  drn::current_view() = &v;
+  const int rc = drn_conv_igemm(desc, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, force_bn, stream);
+  drn::current_view() = nullptr;
+  return rc;
 }

@@ -33,7 +33,7 @@ struct WgradParams {
   int cols_total;       // R*S*C
   int S;
   int PQ, Q;
-  int stride, pad;
+  int stride, pad, pad_w;
   int Kout, C;
   float* dw;
 };
@@ -129,7 +129,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
           const int rem = m0 - img * p.PQ;
           const int op = rem / p.Q;
           const int oq = rem - op * p.Q;
-          const int w0 = oq * p.stride - p.pad, h0 = op * p.stride - p.pad;
+          const int w0 = oq * p.stride - p.pad_w, h0 = op * p.stride - p.pad;
           mbar_wait(empty_bar(stage), phase ^ 1, 0x110 + stage);
           const uint32_t a_dst = sStages + stage * C_::kStageBytes;
           const uint32_t b_dst = a_dst + C_::kABytes;
@@ -252,16 +252,21 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
   p.PQ = d.P * d.Q;
   p.Q = d.Q;
   p.stride = d.stride;
+  const ConvView* view = current_view();
+  const int pad_w_lo = view ? view->pad_w_lo : d.pad_lo, pad_w_hi = view ? view->pad_w_hi : d.pad_hi;
+  long long vstr[3] = {0, 0, 0};
+  if (view) { vstr[0] = view->stride_w; vstr[1] = view->stride_h; vstr[2] = view->stride_n; }
   p.pad = d.pad_lo;
+  p.pad_w = pad_w_lo;
   p.Kout = d.K;
   p.C = d.C;
   p.dw = dw;
 
   CUtensorMap tDY, tX;
   if (int e = tmap_tiled_2d(&tDY, dy, 2, (uint64_t)M, d.K, d.K, kPix, CWA, C_::kRBA)) return e;
-  if (int e = tmap_im2col_nhwc(&tX, x, d.N, d.H, d.W, d.C, -d.pad_lo, -d.pad_lo,
-                               d.pad_hi - (d.R - 1), d.pad_hi - (d.S - 1), d.stride, d.stride, CWB,
-                               kPix, C_::kRBB))
+  if (int e = tmap_im2col_nhwc(&tX, x, d.N, d.H, d.W, d.C, -d.pad_lo, -pad_w_lo,
+                               d.pad_hi - (d.R - 1), pad_w_hi - (d.S - 1), d.stride, d.stride, CWB,
+                               kPix, C_::kRBB, view ? vstr : nullptr))
     return e;
   static bool attr_set = false;
   if (!attr_set) {
@@ -299,4 +304,13 @@ extern "C" int drn_conv_wgrad(const drn_conv_desc* desc, const void* x, const vo
   if (d.K == 32) return dispatch_b<32>(d, x, dy, dw, split_k, st);
   DRN_REQUIRE(d.K % 64 == 0, "conv_wgrad: K must be 16, 32 or a multiple of 64 (got %d)", d.K);
   return dispatch_b<64>(d, x, dy, dw, split_k, st);
+}
+
+extern "C" int drn_conv_wgrad_view(const drn_conv_desc* desc, const drn_conv_view* view, const void* x,
+                                   const void* dy, float* dw, int split_k, void* stream) {
+  drn::ConvView v{view->stride_w, view->stride_h, view->stride_n, view->pad_w_lo, view->pad_w_hi};
+  drn::current_view() = &v;
+  const int rc = drn_conv_wgrad(desc, x, dy, dw, split_k, stream);
+  drn::current_view() = nullptr;
+  return rc;
 }

@@ -23,6 +23,11 @@ int fail(const char* fmt, ...) {
   return 1;
 }
 
+const ConvView*& current_view() {
+  static thread_local const ConvView* v = nullptr;
+  return v;
+}
+
 int num_sms() {
   static int cached[64] = {0};
   int dev = 0;
@@ -106,7 +111,8 @@ int tmap_tiled_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t r
 
 int tmap_im2col_nhwc(CUtensorMap* out, const void* base, int N, int H, int W, int C, int lower_h,
                      int lower_w, int upper_h, int upper_w, int stride_h, int stride_w,
-                     uint32_t channels_per_pixel, uint32_t pixels_per_column, int swizzle_bytes) {
+                     uint32_t channels_per_pixel, uint32_t pixels_per_column, int swizzle_bytes,
+                     const long long* elem_strides) {
   std::call_once(g_driver_once, resolve_driver);
   DRN_REQUIRE(g_encode_im2col != nullptr, "cuTensorMapEncodeIm2col entry point not available");
   DRN_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "tmap_im2col: base not 16B aligned");
@@ -114,6 +120,14 @@ int tmap_im2col_nhwc(CUtensorMap* out, const void* base, int N, int H, int W, in
   DRN_REQUIRE(pixels_per_column <= 1024 && channels_per_pixel <= 256, "tmap_im2col: box too large");
   cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   cuuint64_t gstride[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  if (elem_strides != nullptr) {
+    for (int i = 0; i < 3; ++i) {
+      DRN_REQUIRE(elem_strides[i] > 0 && (elem_strides[i] * 2) % 16 == 0,
+                  "tmap_im2col: view stride %d (%lld elements) must be a positive multiple of 8", i,
+                  elem_strides[i]);
+      gstride[i] = (cuuint64_t)elem_strides[i] * 2;
+    }
+  }
   int lower[2] = {lower_w, lower_h};
   int upper[2] = {upper_w, upper_h};
   cuuint32_t estr[4] = {1, (cuuint32_t)stride_w, (cuuint32_t)stride_h, 1};

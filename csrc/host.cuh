@@ -43,8 +43,19 @@ int tmap_tiled_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t r
 
 // im2col map over an NHWC bf16 tensor. Corners follow the CUDA driver convention:
 // lower = -pad_lo, upper = pad_hi - (filter - 1) (dilation 1).
+// `elem_strides` (optional) = {w, h, n} strides in ELEMENTS for a non-dense (possibly overlapping)
+// view of the tensor; NULL = dense NHWC.
 int tmap_im2col_nhwc(CUtensorMap* out, const void* base, int N, int H, int W, int C, int lower_h,
                      int lower_w, int upper_h, int upper_w, int stride_h, int stride_w,
-                     uint32_t channels_per_pixel, uint32_t pixels_per_column, int swizzle_bytes);
+                     uint32_t channels_per_pixel, uint32_t pixels_per_column, int swizzle_bytes,
+                     const long long* elem_strides = nullptr);
+
+// Optional view of the input tensor used by the *_view entry points (thread-local, set around the
+// ordinary launchers): strides in elements and separate zero padding along W.
+struct ConvView {
+  long long stride_w, stride_h, stride_n;
+  int pad_w_lo, pad_w_hi;
+};
+const ConvView*& current_view();
 
 }  // namespace drn

@@ -92,21 +92,23 @@ __global__ void maxpool_bwd_kernel(const BF8* __restrict__ dy, const U8x8* __res
     float g[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) g[k] = 0.f;
-    for (int r = 0; r < ksize; ++r) {
-      const int hp = h + pad_lo - r;
-      if (hp < 0 || hp % stride != 0) continue;
-      const int p = hp / stride;
-      if (p >= P) continue;
-      for (int s = 0; s < ksize; ++s) {
-        const int wq = w + pad_lo - s;
-        if (wq < 0 || wq % stride != 0) continue;
-        const int q = wq / stride;
-        if (q >= Q) continue;
+    // windows p with p*stride <= h+pad_lo <= p*stride + ksize-1 (at most ceil(ksize/stride)^2 of them)
+    const int hh = h + pad_lo, ww = w + pad_lo;
+    int p_lo = (hh - (ksize - 1) + stride - 1) / stride, p_hi = hh / stride;
+    int q_lo = (ww - (ksize - 1) + stride - 1) / stride, q_hi = ww / stride;
+    if (hh - (ksize - 1) < 0) p_lo = 0;
+    if (ww - (ksize - 1) < 0) q_lo = 0;
+    if (p_hi > P - 1) p_hi = P - 1;
+    if (q_hi > Q - 1) q_hi = Q - 1;
+    for (int p = p_lo; p <= p_hi; ++p) {
+      const int r = hh - p * stride;
+      for (int q = q_lo; q <= q_hi; ++q) {
+        const int s2 = ww - q * stride;
         const long long o = ((n * P + p) * Q + q) * c8 + cg;
         const U8x8 a = argmax[o];
         float d[8];
         unpack8(dy[o], d);
-        const uint8_t me = (uint8_t)(r * ksize + s);
+        const uint8_t me = (uint8_t)(r * ksize + s2);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
           if (a.v[k] == me) g[k] += d[k];

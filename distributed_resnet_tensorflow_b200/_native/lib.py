@@ -23,6 +23,11 @@ class ConvDesc(ctypes.Structure):
                 ("N", "H", "W", "C", "K", "R", "S", "stride", "pad_lo", "pad_hi", "P", "Q")]
 
 
+class ConvView(ctypes.Structure):
+    _fields_ = [("stride_w", ctypes.c_longlong), ("stride_h", ctypes.c_longlong),
+                ("stride_n", ctypes.c_longlong), ("pad_w_lo", ctypes.c_int), ("pad_w_hi", ctypes.c_int)]
+
+
 EPI_PLAIN, EPI_RESADD, EPI_BNBWD = 0, 1, 2
 
 _lib = None
@@ -39,6 +44,8 @@ _SIGNATURES = {
     "drn_num_sms": (_i, []),
     "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
+    "drn_conv_igemm_view": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
+    "drn_conv_wgrad_view": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, _vp, _vp, _i, _vp]),
     "drn_conv_dgrad_scratch_bytes": (_ll, [ctypes.POINTER(ConvDesc)]),
     "drn_conv_dgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _ll, _vp]),
     "drn_conv_dgrad_static": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp]),
@@ -59,7 +66,7 @@ _SIGNATURES = {
     "drn_f32_to_bf16": (_i, [_vp, _vp, _ll, _vp]),
     "drn_mul_inplace_f32": (_i, [_vp, _vp, _ll, _vp]),
     "drn_cifar_augment": (_i, [_vp, _i, _i, _vp, _i, _i, _i, ctypes.c_ulonglong, ctypes.c_uint, _ll, _i, _vp]),
-    "drn_imagenet_prep": (_i, [_vp, _ll, _i, _i, _vp, _vp, _i, _i, _f, _f, _f, _vp]),
+    "drn_imagenet_prep": (_i, [_vp, _ll, _i, _i, _vp, _vp, _i, _i, _f, _f, _f, _i, _i, _vp]),
     "drn_resize_bilinear": (_i, [_vp, _i, _i, _vp, _i, _i, _vp]),
     "drn_crc32c": (ctypes.c_uint32, [_vp, ctypes.c_size_t, ctypes.c_uint32]),
     "drn_tfrecord_index": (_ll, [_vp, ctypes.c_size_t, _vp, _vp, _ll, _i]),
@@ -137,9 +144,41 @@ def add_launches(n: int) -> None:
     _launch_count += n
 
 
+_profile = None   # list of (name, start_event, end_event) while per-call timing is on
+
+
+def start_call_profile() -> None:
+    """Time every subsequent ``call`` with a pair of CUDA events on the current stream
+    (``--profile``: the per-kernel device-time table; do not use while capturing a graph)."""
+    global _profile
+    _profile = []
+
+
+def stop_call_profile():
+    """Returns [(entry point, calls, total_us)] sorted by time and switches timing off."""
+    global _profile
+    import torch
+    torch.cuda.synchronize()
+    agg = {}
+    for name, e0, e1 in _profile or []:
+        c, t = agg.get(name, (0, 0.0))
+        agg[name] = (c + 1, t + e0.elapsed_time(e1) * 1e3)
+    _profile = None
+    return sorted(((n, c, t) for n, (c, t) in agg.items()), key=lambda r: -r[2])
+
+
 def call(name: str, *args) -> None:
     global _launch_count
     _launch_count += 1
+    if _profile is not None:
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn = getattr(load(), name)
+        check(fn(*args), name)
+        e1.record()
+        _profile.append((name, e0, e1))
+        return
     lib = load()
     fn = getattr(lib, name, None)
     if fn is None:

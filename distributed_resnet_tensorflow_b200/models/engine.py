@@ -267,16 +267,27 @@ class NativeResNet:
     def _build(self):
         s, B = self.spec, self.B
         # stem
+        self.stem_view = None
         if s.dataset == "imagenet":
+            # space-to-depth stem: x0 is [B,112,116,16] with two zero pixels left and right of each
+            # row; viewed as [B,112,112,64] with a W stride of 16 elements, the four horizontal
+            # taps of the 4x4 filter become ONE 128-byte TMA row -> a 4x1 convolution, K = 4 x 64.
             self.in_h = s.image_size // 2
-            stem_geom = ConvGeom(B, self.in_h, self.in_h, 16, s.stem.cout, 4, 4, 1, 2, 1)
+            self.in_pitch, self.in_xoff = self.in_h + 4, 2
+            stem_geom = ConvGeom(B, self.in_h, self.in_h, 64, s.stem.cout, 4, 1, 1, 2, 1)
+            self.stem_view = _nl.ConvView(16, self.in_pitch * 16, self.in_h * self.in_pitch * 16, 0, 0)
+            self.x0 = torch.zeros((B, self.in_h, self.in_pitch, 16), dtype=torch.bfloat16, device=self.device)
         else:
             self.in_h = s.image_size
+            self.in_pitch, self.in_xoff = self.in_h, 0
             stem_geom = self._geom(s.stem, cin_override=16)
-        self.x0 = self._act(B, self.in_h, self.in_h, 16)
+            self.x0 = self._act(B, self.in_h, self.in_h, 16)
         self.labels = torch.zeros(B, dtype=torch.int32, device=self.device)
         self.stem = _Conv(s.stem, self, stem_geom, need_dgrad=False)
-        self.y_stem = self._act(B, stem_geom.P, stem_geom.Q, s.stem.cout)
+        if self.stem_view is not None:
+            self.stem.desc.Q = self.in_h       # no padding along W in the view (the borders are data)
+        self.stem_P = self.stem_Q = stem_geom.P
+        self.y_stem = self._act(B, self.stem_P, self.stem_Q, s.stem.cout)
         if s.maxpool:
             hp = (stem_geom.P + 1) // 2
             self.pool_out = self._act(B, hp, hp, s.stem.cout)
@@ -405,6 +416,14 @@ class NativeResNet:
         _nl.call("drn_conv_igemm", ctypes.byref(desc), _p(x), _p(w), _p(y), _p(side), _p(stats),
                  stats.stride(0) if stats is not None else 0, _p(ss), mode, 0, self._st())
 
+    def _stem_conv(self, stats) -> None:
+        if self.stem_view is None:
+            self._conv(self.stem.desc, self.x0, self.stem.w, self.y_stem, stats=stats)
+            return
+        _nl.call("drn_conv_igemm_view", ctypes.byref(self.stem.desc), ctypes.byref(self.stem_view), _p(self.x0),
+                 _p(self.stem.w), _p(self.y_stem), 0, _p(stats), stats.stride(0) if stats is not None else 0,
+                 0, EPI_PLAIN, 0, self._st())
+
     def _wgrad(self, conv: _Conv, x, dy):
         _nl.call("drn_conv_wgrad", ctypes.byref(conv.desc), _p(x), _p(dy), _p(conv.dw), 0, self._st())
 
@@ -440,18 +459,17 @@ class NativeResNet:
             self._stats_arena.zero_()
         first_bn = self.blocks[0]["bn0"]
         if s.maxpool:
-            self._conv(self.stem.desc, self.x0, self.stem.w, self.y_stem)
+            self._stem_conv(None)
             g = self.stem.g
             hp = self.pool_out.shape[1]
             _nl.call("drn_maxpool_fwd", _p(self.y_stem), _p(self.pool_out), _p(self.pool_arg), self.B,
-                     g.P, g.Q, g.K, 3, 2, 0, hp, hp, st)
+                     self.stem_P, self.stem_Q, g.K, 3, 2, 0, hp, hp, st)
             if training:
                 _nl.call("drn_bn_stats", _p(self.pool_out), _p(first_bn.fstats), first_bn.fstats.stride(0),
                          self.pool_out.numel() // g.K, g.K, st)
             x = self.pool_out
         else:
-            self._conv(self.stem.desc, self.x0, self.stem.w, self.y_stem,
-                       stats=first_bn.fstats if training else None)
+            self._stem_conv(first_bn.fstats if training else None)
             x = self.y_stem
         for i, b in enumerate(self.blocks):
             nxt = self.blocks[i + 1]["bn0"] if i + 1 < len(self.blocks) else self.final_bn
@@ -567,11 +585,15 @@ class NativeResNet:
             sg = self.stem.g
             hp = self.pool_out.shape[1]
             d_i, d_stem = self._get(self.y_stem)
-            _nl.call("drn_maxpool_bwd", _p(g), _p(self.pool_arg), _p(d_stem), self.B, sg.P, sg.Q,
+            _nl.call("drn_maxpool_bwd", _p(g), _p(self.pool_arg), _p(d_stem), self.B, self.stem_P, self.stem_Q,
                      sg.K, 3, 2, 0, hp, hp, st)
             self._put(g_i)
             g_i, g = d_i, d_stem
-        self._wgrad(self.stem, self.x0, g)
+        if self.stem_view is not None:
+            _nl.call("drn_conv_wgrad_view", ctypes.byref(self.stem.desc), ctypes.byref(self.stem_view),
+                     _p(self.x0), _p(g), _p(self.stem.dw), 0, st)
+        else:
+            self._wgrad(self.stem, self.x0, g)
         self._put(g_i)
         if self.stem_mask is not None:
             _nl.call("drn_mul_inplace_f32", _p(self.stem.dw), _p(self.stem_mask),
@@ -669,7 +691,10 @@ class NativeResNet:
         else:
             pad = 13
         x = torch.nn.functional.pad(x, (0, pad))
-        self.x0.copy_(x.to(torch.bfloat16))
+        if self.in_pitch != self.in_h:
+            self.x0[:, :, self.in_xoff:self.in_xoff + self.in_h, :].copy_(x.to(torch.bfloat16))
+        else:
+            self.x0.copy_(x.to(torch.bfloat16))
         self.labels.copy_(labels.to(self.device, torch.int32))
 
     # ---- convenience: one full step (no graph) ----------------------------------------------------

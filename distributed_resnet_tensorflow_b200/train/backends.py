@@ -257,6 +257,9 @@ class NativeBackend:
         i, l, c = self._stage(images_u8, labels, crop)
         return self.trainer.train_step(i, l, lr, c)
 
+    def profile_step(self) -> str:
+        return self.trainer.profile_step()
+
     def eval_batch(self, images_u8, labels, crop=None):
         i, l, c = self._stage(images_u8, labels, crop)
         return self.trainer.eval_batch(i, l, c)

@@ -246,6 +246,8 @@ def train(cfg: Config) -> Dict[str, float]:
             continue
         metrics = be.train_step(imgs, labs, lr, crop)
         local_steps += 1
+        if t.profile and local_steps == 3 and ctx.is_chief and not ctx.distributed and hasattr(be, "profile_step"):
+            log.info("per-kernel device time of one training step:\n%s", be.profile_step())
         step = be.global_step
         sched.after_step(step)
         if step % t.log_every == 0:

@@ -111,7 +111,7 @@ class NativeTrainer:
         if self.spec.dataset == "imagenet":
             _nl.call("drn_imagenet_prep", _p(self._dev_u8[slot]), self.img_bytes, self.src_hw, self.src_hw,
                      _p(self._dev_crop[slot]), _p(e.x0), self.B, self.spec.image_size, VGG_MEANS[0],
-                     VGG_MEANS[1], VGG_MEANS[2], st)
+                     VGG_MEANS[1], VGG_MEANS[2], e.in_pitch, e.in_xoff, st)
         else:
             _nl.call("drn_cifar_augment", _p(self._dev_u8[slot]), self.img_bytes, 0, _p(e.x0), self.B,
                      self.cifar_pad, 1 if training else 0, self.seed, step & 0xffffffff,
@@ -185,6 +185,24 @@ class NativeTrainer:
         torch.cuda.synchronize(self.device)
         self._restore(snapshot)   # capture does not execute, but keep state exact regardless
         self._graph = g
+
+    def profile_step(self) -> str:
+        """Per-entry-point device time of one eager training step on the currently staged input
+        (state is restored afterwards). The capability behind ``--profile``."""
+        snap = self._snapshot()
+        self._step_body()                      # warm
+        torch.cuda.synchronize(self.device)
+        self._restore(snap)
+        _nl.start_call_profile()
+        self._step_body()
+        rows = _nl.stop_call_profile()
+        self._restore(snap)
+        total = sum(r[2] for r in rows) or 1.0
+        lines = [f"{'entry point':28s} {'calls':>6s} {'total us':>10s} {'share':>7s}"]
+        for name, calls, us in rows:
+            lines.append(f"{name:28s} {calls:6d} {us:10.1f} {100 * us / total:6.1f}%")
+        lines.append(f"{'sum of kernels':28s} {sum(r[1] for r in rows):6d} {total:10.1f}")
+        return "\n".join(lines)
 
     def launches_per_step(self) -> int:
         """Kernels of libdrn_b200 enqueued per training step (graph body + augmentation)."""

@@ -58,6 +58,17 @@ int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const void* w, void
                    const void* side, float* stats, int stats_ld, const void* bn_scale_shift,
                    int mode, int force_bn, void* stream);
 
+/* The same two kernels over a strided (possibly overlapping) view of x: element strides between
+ * pixels along W, rows and images, and zero padding along W given separately from desc->pad_*
+ * (which then applies to H only). desc->W / desc->Q describe the view. */
+typedef struct {
+  long long stride_w, stride_h, stride_n; /* in elements, multiples of 8 */
+  int pad_w_lo, pad_w_hi;
+} drn_conv_view;
+int drn_conv_igemm_view(const drn_conv_desc* desc, const drn_conv_view* view, const void* x,
+                        const void* w, void* y, const void* side, float* stats, int stats_ld,
+                        const void* bn_scale_shift, int mode, int force_bn, void* stream);
+
 /* Data gradient (K2) of the convolution described by `desc` (FORWARD geometry):
  *   dx[N,H,W,C] = sum_{k,r,s} dy[N,P,Q,K] (x) w,  given w_dgrad = drn_weight_prep_dgrad(w).
  * Runs the implicit-GEMM kernel above on the equivalent stride-1 problem; for stride > 1 dy is first
@@ -87,6 +98,9 @@ int drn_conv_dgrad_static(const drn_conv_desc* desc, const void* dy, const void*
 int drn_conv_wgrad(const drn_conv_desc* desc, const void* x, const void* dy, float* dw,
                    int split_k, void* stream);
 
+
+int drn_conv_wgrad_view(const drn_conv_desc* desc, const drn_conv_view* view, const void* x,
+                        const void* dy, float* dw, int split_k, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * BatchNorm + ReLU (reference: batch_norm_relu, resnet_model_official.py:41-50; ops K5-K9)
@@ -156,9 +170,11 @@ int drn_mul_inplace_f32(float* a, const float* b, long long n, void* stream);
 int drn_cifar_augment(const void* records, int record_stride, int image_offset, void* out, int B,
                       int pad, int training, unsigned long long seed, unsigned int step,
                       long long index_base, int cpad, void* stream);
+/* out is [B, crop/2, out_pitch, 16] bf16; pixels land at columns out_xoff .. out_xoff+crop/2-1
+ * (out_pitch 0 = dense). Border columns are never written: keep them zero. */
 int drn_imagenet_prep(const void* src, long long image_stride, int src_h, int src_w,
                       const int* crop_yx_flip, void* out, int B, int crop, float mean_r,
-                      float mean_g, float mean_b, void* stream);
+                      float mean_g, float mean_b, int out_pitch, int out_xoff, void* stream);
 int drn_resize_bilinear(const void* src, int sh, int sw, float* dst, int dh, int dw, void* stream);
 
 /* ---------------------------------------------------------------------------------------------

@@ -224,8 +224,14 @@ def test_imagenet_prep_matches_cpu_oracle():
     d, c = torch.from_numpy(imgs).cuda(), torch.from_numpy(crop).cuda()
     out = torch.empty((B, S // 2, S // 2, 16), dtype=torch.bfloat16, device="cuda")
     m = preprocess.VGG_MEANS_01
-    nl.call("drn_imagenet_prep", _p(d), S * S * 3, S, S, _p(c), _p(out), B, S, float(m[0]), float(m[1]), float(m[2]), _st())
+    nl.call("drn_imagenet_prep", _p(d), S * S * 3, S, S, _p(c), _p(out), B, S, float(m[0]), float(m[1]), float(m[2]), 0, 0, _st())
     got = out.float().cpu().numpy()
+    # the zero-bordered layout the stem reads: pitch 116 pixels, image at column 2
+    outp = torch.zeros((B, S // 2, S // 2 + 4, 16), dtype=torch.bfloat16, device="cuda")
+    nl.call("drn_imagenet_prep", _p(d), S * S * 3, S, S, _p(c), _p(outp), B, S, float(m[0]), float(m[1]), float(m[2]),
+            S // 2 + 4, 2, _st())
+    gotp = outp.float().cpu().numpy()
+    assert np.all(gotp[:, :, :2] == 0) and np.all(gotp[:, :, -2:] == 0) and np.array_equal(gotp[:, :, 2:-2], got)
     for b in range(B):
         ref = preprocess.space_to_depth16(preprocess.imagenet_prep_oracle(imgs[b], bool(crop[b, 2])))
         assert np.abs(got[b] - ref).max() < 0.005
