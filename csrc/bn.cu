@@ -83,17 +83,51 @@ __global__ void bn_apply_kernel(const BF8* __restrict__ y, const float2* __restr
   float2 ss[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) ss[k] = __ldg(scale_shift + cg * 8 + k);
+  for (; i + stride < n_vec; i += 2 * stride) {
+    const BF8 y0 = y[i], y1 = y[i + stride];
+    BF8 a0 = y0, a1 = y1;
+    if (addend != nullptr) {
+      a0 = addend[i];
+      a1 = addend[i + stride];
+    }
+    float f0[8], f1[8];
+    unpack8(y0, f0);
+    unpack8(y1, f1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      f0[k] = fmaf(f0[k], ss[k].x, ss[k].y);
+      f1[k] = fmaf(f1[k], ss[k].x, ss[k].y);
+    }
+    if (addend != nullptr) {
+      float t0[8], t1[8];
+      unpack8(a0, t0);
+      unpack8(a1, t1);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        f0[k] += t0[k];
+        f1[k] += t1[k];
+      }
+    }
+    if (relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        f0[k] = fmaxf(f0[k], 0.f);
+        f1[k] = fmaxf(f1[k], 0.f);
+      }
+    }
+    out[i] = pack8(f0);
+    out[i + stride] = pack8(f1);
+  }
   for (; i < n_vec; i += stride) {
     float f[8];
     unpack8(y[i], f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], ss[k].x, ss[k].y);
     if (addend != nullptr) {
       float ad[8];
       unpack8(addend[i], ad);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], ss[k].x, ss[k].y) + ad[k];
-    } else {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], ss[k].x, ss[k].y);
+      for (int k = 0; k < 8; ++k) f[k] += ad[k];
     }
     if (relu) {
 #pragma unroll
@@ -248,18 +282,48 @@ __global__ void bn_bwd_apply_kernel(const BF8* __restrict__ dm, const BF8* __res
   float4 cf[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) cf[k] = __ldg(coef + cg * 8 + k);
+  // two independent vectors per iteration: more loads in flight per thread
+  for (; i + stride < n_vec; i += 2 * stride) {
+    const BF8 d0 = dm[i], d1 = dm[i + stride];
+    const BF8 y0 = y[i], y1 = y[i + stride];
+    BF8 a0 = d0, a1 = d1;
+    if (addend != nullptr) {
+      a0 = addend[i];
+      a1 = addend[i + stride];
+    }
+    float g0[8], g1[8], t0[8], t1[8];
+    unpack8(d0, g0);
+    unpack8(d1, g1);
+    unpack8(y0, t0);
+    unpack8(y1, t1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      g0[k] = fmaf(cf[k].x, g0[k], fmaf(cf[k].y, t0[k], cf[k].z));
+      g1[k] = fmaf(cf[k].x, g1[k], fmaf(cf[k].y, t1[k], cf[k].z));
+    }
+    if (addend != nullptr) {
+      unpack8(a0, t0);
+      unpack8(a1, t1);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        g0[k] += t0[k];
+        g1[k] += t1[k];
+      }
+    }
+    dy[i] = pack8(g0);
+    dy[i + stride] = pack8(g1);
+  }
   for (; i < n_vec; i += stride) {
     float g[8], yy[8];
     unpack8(dm[i], g);
     unpack8(y[i], yy);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = fmaf(cf[k].x, g[k], fmaf(cf[k].y, yy[k], cf[k].z));
     if (addend != nullptr) {
       float ad[8];
       unpack8(addend[i], ad);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] = fmaf(cf[k].x, g[k], fmaf(cf[k].y, yy[k], cf[k].z)) + ad[k];
-    } else {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] = fmaf(cf[k].x, g[k], fmaf(cf[k].y, yy[k], cf[k].z));
+      for (int k = 0; k < 8; ++k) g[k] += ad[k];
     }
     dy[i] = pack8(g);
   }

@@ -20,6 +20,8 @@
 // transposed filter bank (see optim.cu: drn_weight_prep) as Wt.
 //
 // Covers reference ops K1, K2, K4, K9 (as producer of statistics), K10.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "host.cuh"
 #include "../include/drn_b200.h"
@@ -476,6 +478,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
   }
 }
 
+inline int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
 template <int KC, int BN>
 int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, const void* side,
                 float* stats, int stats_ld, const void* bn_scale_shift, int mode,
@@ -502,7 +509,7 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   p.pad_h = d.pad_lo;
   p.pad_w = pad_w_lo;
   p.mode = mode;
-  p.n_res = mode == DRN_EPI_PLAIN ? 0 : (BN >= 256 ? 3 : 4);
+  p.n_res = mode == DRN_EPI_PLAIN ? 0 : (env_int("DRN_NRES", 2));
   p.n_stages = C_::stages_for(p.n_res);
   if (p.n_stages < 2) return fail("conv_igemm: shared memory plan does not fit (KC=%d BN=%d)", KC, BN);
   const int smem_bytes = C_::smem_for(p.n_res, p.n_stages);
@@ -575,7 +582,7 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
   if (bn == 0) {
     // 256-wide tiles leave room for only two pipeline stages next to the side-input ring: keep
     // them for shallow reductions, use 128 when the K loop is long
-    const bool deep_k = d.R * d.S * d.C > 256;
+    const bool deep_k = d.R * d.S * d.C > env_int("DRN_DEEPK", 256);
     if (d.K % 256 == 0 && !(mode != DRN_EPI_PLAIN && deep_k)) bn = 256;
     else if (d.K % 128 == 0) bn = 128;
     else if (d.K % 64 == 0) bn = 64;
