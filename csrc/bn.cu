@@ -329,6 +329,141 @@ __global__ void bn_bwd_apply_kernel(const BF8* __restrict__ dm, const BF8* __res
   }
 }
 
+
+// ---- fused variants: the per-channel "finalize" arithmetic is redone by every thread for its own
+// 8 channels (a few dozen flops) instead of being a separate tiny launch; the threads of block 0
+// publish the per-channel results other kernels need (scale/shift, mean/invstd, moving averages,
+// dgamma/dbeta). Saves ~100 launches per ResNet-50 step.
+__global__ void bn_finalize_apply_kernel(const BF8* __restrict__ y, const float* __restrict__ stats,
+                                         int stats_ld, float inv_count, float unbias,
+                                         const float* __restrict__ gamma, const float* __restrict__ beta,
+                                         float* __restrict__ run_mean, float* __restrict__ run_var,
+                                         float one_minus_decay, float eps,
+                                         float2* __restrict__ scale_shift, float2* __restrict__ mean_invstd,
+                                         BF8* __restrict__ out, long long n_vec, int c8, int relu) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cg = (int)(i % c8);
+  const bool publish = blockIdx.x == 0 && (int)threadIdx.x < c8;
+  float2 ss[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cg * 8 + k;
+    const float mean = __ldg(stats + c) * inv_count;
+    const float var = fmaxf(fmaf(-mean, mean, __ldg(stats + stats_ld + c) * inv_count), 0.f);
+    const float invstd = rsqrtf(var + eps);
+    const float sc = __ldg(gamma + c) * invstd;
+    ss[k] = make_float2(sc, fmaf(-mean, sc, __ldg(beta + c)));
+    if (publish) {
+      scale_shift[c] = ss[k];
+      mean_invstd[c] = make_float2(mean, invstd);
+      if (run_mean != nullptr) {
+        run_mean[c] -= (run_mean[c] - mean) * one_minus_decay;
+        run_var[c] -= (run_var[c] - var * unbias) * one_minus_decay;
+      }
+    }
+  }
+  for (; i + stride < n_vec; i += 2 * stride) {
+    const BF8 y0 = y[i], y1 = y[i + stride];
+    float f0[8], f1[8];
+    unpack8(y0, f0);
+    unpack8(y1, f1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      f0[k] = fmaf(f0[k], ss[k].x, ss[k].y);
+      f1[k] = fmaf(f1[k], ss[k].x, ss[k].y);
+      if (relu) {
+        f0[k] = fmaxf(f0[k], 0.f);
+        f1[k] = fmaxf(f1[k], 0.f);
+      }
+    }
+    out[i] = pack8(f0);
+    out[i + stride] = pack8(f1);
+  }
+  for (; i < n_vec; i += stride) {
+    float f[8];
+    unpack8(y[i], f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      f[k] = fmaf(f[k], ss[k].x, ss[k].y);
+      if (relu) f[k] = fmaxf(f[k], 0.f);
+    }
+    out[i] = pack8(f);
+  }
+}
+
+__global__ void bn_bwd_finalize_apply_kernel(const BF8* __restrict__ dm, const BF8* __restrict__ y,
+                                             const float* __restrict__ stats, int stats_ld,
+                                             float inv_count, const float* __restrict__ gamma,
+                                             const float2* __restrict__ mean_invstd,
+                                             float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                             const BF8* __restrict__ addend, BF8* __restrict__ dy,
+                                             long long n_vec, int c8) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cg = (int)(i % c8);
+  const bool publish = blockIdx.x == 0 && (int)threadIdx.x < c8;
+  float ca[8], cb[8], cc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cg * 8 + k;
+    const float s1 = __ldg(stats + c), s2 = __ldg(stats + stats_ld + c);
+    const float2 mi = __ldg(mean_invstd + c);
+    const float dg = mi.y * (s2 - mi.x * s1);
+    if (publish && dgamma != nullptr) {
+      dgamma[c] += dg;
+      dbeta[c] += s1;
+    }
+    ca[k] = __ldg(gamma + c) * mi.y;
+    cb[k] = -ca[k] * mi.y * dg * inv_count;
+    cc[k] = -ca[k] * s1 * inv_count - cb[k] * mi.x;
+  }
+  for (; i + stride < n_vec; i += 2 * stride) {
+    const BF8 d0 = dm[i], d1 = dm[i + stride];
+    const BF8 y0 = y[i], y1 = y[i + stride];
+    BF8 a0 = d0, a1 = d1;
+    if (addend != nullptr) {
+      a0 = addend[i];
+      a1 = addend[i + stride];
+    }
+    float g0[8], g1[8], t0[8], t1[8];
+    unpack8(d0, g0);
+    unpack8(d1, g1);
+    unpack8(y0, t0);
+    unpack8(y1, t1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      g0[k] = fmaf(ca[k], g0[k], fmaf(cb[k], t0[k], cc[k]));
+      g1[k] = fmaf(ca[k], g1[k], fmaf(cb[k], t1[k], cc[k]));
+    }
+    if (addend != nullptr) {
+      unpack8(a0, t0);
+      unpack8(a1, t1);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        g0[k] += t0[k];
+        g1[k] += t1[k];
+      }
+    }
+    dy[i] = pack8(g0);
+    dy[i + stride] = pack8(g1);
+  }
+  for (; i < n_vec; i += stride) {
+    float g[8], yy[8];
+    unpack8(dm[i], g);
+    unpack8(y[i], yy);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = fmaf(ca[k], g[k], fmaf(cb[k], yy[k], cc[k]));
+    if (addend != nullptr) {
+      float ad[8];
+      unpack8(addend[i], ad);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += ad[k];
+    }
+    dy[i] = pack8(g);
+  }
+}
+
 int check_c(int C, const char* who) {
   const int c8 = C / 8;
   if (C % 8 != 0 || c8 > kThreads || (c8 & (c8 - 1)) != 0)
@@ -429,6 +564,37 @@ extern "C" int drn_bn_bwd_apply(const void* dm, const void* y, const void* coef,
   bn_bwd_apply_kernel<<<ew_grid(n_vec), kThreads, 0, (cudaStream_t)stream>>>(
       (const BF8*)dm, (const BF8*)y, (const float4*)coef, (const BF8*)addend, (BF8*)dy, n_vec,
       C / 8);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// bn_finalize + bn_apply in one launch (training forward).
+extern "C" int drn_bn_finalize_apply(const void* y, const float* stats, int stats_ld, long long count,
+                                     const float* gamma, const float* beta, float* run_mean,
+                                     float* run_var, float decay, float eps, void* scale_shift,
+                                     void* mean_invstd, void* out, int C, int relu, void* stream) {
+  if (int e = check_c(C, "bn_finalize_apply")) return e;
+  DRN_REQUIRE(count > 0, "bn_finalize_apply: count must be positive");
+  const float unbias = count > 1 ? (float)((double)count / (double)(count - 1)) : 1.f;
+  const long long n_vec = count * (C / 8);
+  bn_finalize_apply_kernel<<<ew_grid(n_vec), kThreads, 0, (cudaStream_t)stream>>>(
+      (const BF8*)y, stats, stats_ld, (float)(1.0 / (double)count), unbias, gamma, beta, run_mean,
+      run_var, 1.f - decay, eps, (float2*)scale_shift, (float2*)mean_invstd, (BF8*)out, n_vec, C / 8,
+      relu);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// bn_bwd_finalize + bn_bwd_apply in one launch.
+extern "C" int drn_bn_bwd_finalize_apply(const void* dm, const void* y, const float* stats,
+                                         int stats_ld, long long count, const float* gamma,
+                                         const void* mean_invstd, float* dgamma, float* dbeta,
+                                         const void* addend, void* dy, int C, void* stream) {
+  if (int e = check_c(C, "bn_bwd_finalize_apply")) return e;
+  const long long n_vec = count * (C / 8);
+  bn_bwd_finalize_apply_kernel<<<ew_grid(n_vec), kThreads, 0, (cudaStream_t)stream>>>(
+      (const BF8*)dm, (const BF8*)y, stats, stats_ld, (float)(1.0 / (double)count), gamma,
+      (const float2*)mean_invstd, dgamma, dbeta, (const BF8*)addend, (BF8*)dy, n_vec, C / 8);
   DRN_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -13,6 +13,8 @@
 // into TMEM and adds the fp32 tile into dW with vector red.global (split-K).
 //
 // Replaces cudnnConvolutionBackwardFilter in the reference's autodiff graph (op K3).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "host.cuh"
 #include "../include/drn_b200.h"
@@ -239,7 +241,12 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
   int splits = split_k;
   if (splits <= 0) {
     // ~2 waves of CTAs, but keep at least 8 chunks (512 pixels) per CTA
-    splits = (2 * num_sms() + units - 1) / units;
+    // measured on B200 (bench/sweep_wgrad.sh): 1x1 layers are bound by the fp32 red.global traffic
+    // (splits x weights), one wave of CTAs is best; 3x3 layers are bound by L2->SM im2col traffic
+    // and balance better with two waves.
+    static const int waves_env = getenv("DRN_WGRAD_WAVES") ? atoi(getenv("DRN_WGRAD_WAVES")) : 0;
+    const int waves = waves_env > 0 ? waves_env : (d.R * d.S > 1 ? 2 : 1);
+    splits = (waves * num_sms() + units - 1) / units;
     int max_splits = p.chunks_total / 8;
     if (max_splits < 1) max_splits = 1;
     if (splits > max_splits) splits = max_splits;

@@ -72,6 +72,42 @@ __global__ void weight_prep_dgrad_kernel(const __nv_bfloat16* __restrict__ src,
   }
 }
 
+// All layers in one launch: block -> (layer, tap, k-tile, c-tile) through a table of tile offsets.
+struct PrepEntry {
+  long long src_off, dst_off;  // element offsets into the bf16 weight arena / the dgrad-bank arena
+  int K, RS, C, tile_begin;    // tile_begin = first block index of this layer
+};
+__global__ void weight_prep_dgrad_batched_kernel(const __nv_bfloat16* __restrict__ src_base,
+                                                 __nv_bfloat16* __restrict__ dst_base,
+                                                 const PrepEntry* __restrict__ table, int n_layers) {
+  __shared__ __nv_bfloat16 tile[32][33];
+  // binary search: last layer whose tile_begin <= blockIdx.x
+  int lo = 0, hi = n_layers - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (table[mid].tile_begin <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+  }
+  const PrepEntry e = table[lo];
+  int t = blockIdx.x - e.tile_begin;
+  const int ct = (e.C + 31) / 32, kt = (e.K + 31) / 32;
+  const int c0 = (t % ct) * 32;
+  t /= ct;
+  const int k0 = (t % kt) * 32;
+  const int tap = t / kt;
+  const __nv_bfloat16* src = src_base + e.src_off;
+  __nv_bfloat16* dst = dst_base + e.dst_off;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int k = k0 + j, c = c0 + threadIdx.x;
+    if (k < e.K && c < e.C) tile[j][threadIdx.x] = src[((long long)k * e.RS + tap) * e.C + c];
+  }
+  __syncthreads();
+  const int ftap = e.RS - 1 - tap;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    const int c = c0 + j, k = k0 + threadIdx.x;
+    if (k < e.K && c < e.C) dst[((long long)c * e.RS + ftap) * e.K + k] = tile[threadIdx.x][j];
+  }
+}
+
 // out[n, p*s, q*s, :] = dy[n, p, q, :], zeros elsewhere. 8 channels per thread.
 __global__ void upsample_zero_kernel(const uint4* __restrict__ dy, uint4* __restrict__ out, int N,
                                      int P, int Q, int U, int V, int c8, int stride) {
@@ -162,6 +198,19 @@ extern "C" int drn_f32_to_bf16(const float* src, void* dst, long long n, void* s
 // a[i] *= b[i]  (used to keep the structurally-zero taps of the space-to-depth stem filter at zero)
 extern "C" int drn_mul_inplace_f32(float* a, const float* b, long long n, void* stream) {
   mul_inplace_kernel<<<ew_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(a, b, n);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Flipped/transposed dgrad banks of ALL layers in one launch. `table` is a device array of
+// n_layers entries {int64 src_off, int64 dst_off, int32 K, RS, C, tile_begin} (32 bytes each) with
+// tile_begin the running sum of RS * ceil(K/32) * ceil(C/32); total_tiles is the grand total.
+extern "C" int drn_weight_prep_dgrad_batched(const void* w_arena, void* dgrad_arena, const void* table,
+                                             int n_layers, int total_tiles, void* stream) {
+  static_assert(sizeof(PrepEntry) == 32, "PrepEntry layout is part of the ABI");
+  DRN_REQUIRE(n_layers > 0 && total_tiles > 0, "weight_prep_dgrad_batched: empty table");
+  weight_prep_dgrad_batched_kernel<<<total_tiles, dim3(32, 8), 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)w_arena, (__nv_bfloat16*)dgrad_arena, (const PrepEntry*)table, n_layers);
   DRN_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -50,6 +50,8 @@ _SIGNATURES = {
     "drn_conv_dgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _ll, _vp]),
     "drn_conv_dgrad_static": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp]),
     "drn_bn_finalize": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _i, _vp]),
+    "drn_bn_finalize_apply": (_i, [_vp, _vp, _i, _ll, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _i, _i, _vp]),
+    "drn_bn_bwd_finalize_apply": (_i, [_vp, _vp, _vp, _i, _ll, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "drn_bn_inference_params": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _i, _vp]),
     "drn_bn_apply": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp]),
     "drn_bn_stats": (_i, [_vp, _vp, _i, _ll, _i, _vp]),
@@ -62,6 +64,7 @@ _SIGNATURES = {
     "drn_softmax_xent": (_i, [_vp, _i, _vp, _vp, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp]),
     "drn_sgd_momentum": (_i, [_vp, _vp, _vp, _vp, _ll, _vp, _vp, _i, _vp]),
     "drn_weight_prep_dgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "drn_weight_prep_dgrad_batched": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "drn_upsample_zero": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "drn_f32_to_bf16": (_i, [_vp, _vp, _ll, _vp]),
     "drn_mul_inplace_f32": (_i, [_vp, _vp, _ll, _vp]),

@@ -193,8 +193,7 @@ class _Conv:
         self.dg = None
         self.up = None
         if need_dgrad:
-            self.wd = torch.zeros(geom.K * geom.R * geom.S * geom.C, dtype=torch.bfloat16,
-                                  device=eng.device)
+            self.wd = eng.alloc_dgrad_bank(name, geom.K * geom.R * geom.S * geom.C)
             self.dg = geom.dgrad_geom()
             self.dg_desc = self.dg.desc()
             if geom.stride > 1 and geom.R > 1:
@@ -231,6 +230,9 @@ class NativeResNet:
         self._stats_chunks: List[torch.Tensor] = []
         self._stats_arena = torch.zeros(2 * 2 * sum(b.channels for b in spec.bns()) * 2 + 4096, device=dev)
         self._stats_off = 0
+        self._wd_arena = torch.zeros(self.layout.total + 64 * len(self.layout.order), dtype=torch.bfloat16, device=dev)
+        self._wd_off = 0
+        self._wd_entries: List[Tuple[str, int]] = []
         m = self.layout.stem_mask()
         self.stem_mask = torch.from_numpy(m).to(dev).reshape(-1) if m is not None else None
         self._build()
@@ -248,6 +250,15 @@ class NativeResNet:
 
     def shadow_view(self, name):
         return self._view(self.shadow, name)
+
+    def alloc_dgrad_bank(self, name: str, numel: int) -> torch.Tensor:
+        """Slice of the arena holding the flipped/transposed filter banks of all layers (one
+        batched kernel refreshes them after every update)."""
+        off = self._wd_off
+        self._wd_off = _round_up(off + numel, 64)
+        assert self._wd_off <= self._wd_arena.numel()
+        self._wd_entries.append((name, off))
+        return self._wd_arena[off:off + numel]
 
     def alloc_stats(self, C: int) -> torch.Tensor:
         off = self._stats_off
@@ -304,7 +315,7 @@ class NativeResNet:
         self.dense_desc = self.dense_geom.desc()
         self.dense_w = self.shadow_view("dense/kernel")
         self.dense_dw = self.grad_view("dense/kernel")
-        self.dense_wd = torch.zeros(kp * s.dense_in, dtype=torch.bfloat16, device=self.device)
+        self.dense_wd = self.alloc_dgrad_bank("dense/kernel", kp * s.dense_in)
         self.dense_dgeom = ConvGeom(B, 1, 1, kp, s.dense_in, 1, 1, 1, 0, 0)
         self.dense_ddesc = self.dense_dgeom.desc()
         self.dense_bias = self.param_view("dense/bias")
@@ -403,14 +414,29 @@ class NativeResNet:
         _nl.call("drn_f32_to_bf16", _p(self.master), _p(self.shadow), self.layout.total, st)
         self.prep_dgrad_weights()
 
+    def _build_prep_table(self) -> None:
+        rows, tiles = [], 0
+        for name, dst_off in self._wd_entries:
+            e = self.layout.entries[name]
+            if e.kind == "dense_kernel":
+                K, RS, C = e.dev_shape[0], 1, e.dev_shape[1]
+            else:
+                K, RS, C = e.dev_shape[0], e.dev_shape[1] * e.dev_shape[2], e.dev_shape[3]
+            rows.append((e.offset, dst_off, K, RS, C, tiles))
+            tiles += RS * ((K + 31) // 32) * ((C + 31) // 32)
+        tab = np.zeros(len(rows), dtype=[("src", "<i8"), ("dst", "<i8"), ("K", "<i4"), ("RS", "<i4"),
+                                         ("C", "<i4"), ("tb", "<i4")])
+        for i, r in enumerate(rows):
+            tab[i] = r
+        self._prep_table = torch.from_numpy(tab.view(np.uint8).copy()).to(self.device)
+        self._prep_layers, self._prep_tiles = len(rows), tiles
+
     def prep_dgrad_weights(self) -> None:
-        st = self._st()
-        for c in self._all_convs():
-            if c.wd is not None:
-                g = c.g
-                _nl.call("drn_weight_prep_dgrad", _p(c.w), _p(c.wd), g.K, g.R, g.S, g.C, st)
-        _nl.call("drn_weight_prep_dgrad", _p(self.dense_w), _p(self.dense_wd), self.kp, 1, 1,
-                 self.spec.dense_in, st)
+        """Flipped + transposed bf16 banks of every layer that has a data gradient (one launch)."""
+        if not hasattr(self, "_prep_table"):
+            self._build_prep_table()
+        _nl.call("drn_weight_prep_dgrad_batched", _p(self.shadow), _p(self._wd_arena), _p(self._prep_table),
+                 self._prep_layers, self._prep_tiles, self._st())
 
     def _conv(self, desc, x, w, y, side=None, stats=None, ss=None, mode=EPI_PLAIN):
         _nl.call("drn_conv_igemm", ctypes.byref(desc), _p(x), _p(w), _p(y), _p(side), _p(stats),
@@ -436,6 +462,17 @@ class NativeResNet:
         else:
             _nl.call("drn_bn_inference_params", _p(bn.gamma), _p(bn.beta), _p(bn.run_mean),
                      _p(bn.run_var), BN_EPS, _p(bn.ss), bn.C, st)
+
+    def _bn_fwd(self, bn: _BN, y, out, training: bool):
+        """a = relu(bn(y)): statistics -> scale/shift -> apply, one launch in training mode."""
+        count = y.numel() // bn.C
+        if training:
+            _nl.call("drn_bn_finalize_apply", _p(y), _p(bn.fstats), bn.fstats.stride(0), count, _p(bn.gamma),
+                     _p(bn.beta), _p(bn.run_mean), _p(bn.run_var), BN_DECAY, BN_EPS, _p(bn.ss), _p(bn.mi),
+                     _p(out), bn.C, 1, self._st())
+        else:
+            self._bn_finalize(bn, count, False)
+            self._bn_apply(bn, y, out)
 
     def _bn_apply(self, bn: _BN, y, out):
         M = y.numel() // bn.C
@@ -484,8 +521,7 @@ class NativeResNet:
     def _block_fwd(self, b: dict, x, next_bn: _BN, training: bool):
         bn0 = b["bn0"]
         b["x"] = x
-        self._bn_finalize(bn0, x.numel() // bn0.C, training)
-        self._bn_apply(bn0, x, b["a0"])
+        self._bn_fwd(bn0, x, b["a0"], training)
         shortcut = x
         if "proj" in b:
             pj = b["proj"]
@@ -502,8 +538,7 @@ class NativeResNet:
             else:
                 bn = b["bns"][i]
                 self._conv(c.desc, h, c.w, y, stats=bn.fstats if training else None)
-                self._bn_finalize(bn, y.numel() // bn.C, training)
-                self._bn_apply(bn, y, b["acts"][i])
+                self._bn_fwd(bn, y, b["acts"][i], training)
                 h = b["acts"][i]
         return b["ys"][-1]
 
@@ -604,9 +639,8 @@ class NativeResNet:
     def _bn_bwd(self, bn: _BN, dm, y, addend, out):
         st = self._st()
         count = y.numel() // bn.C
-        _nl.call("drn_bn_bwd_finalize", _p(bn.bstats), bn.bstats.stride(0), count, _p(bn.gamma),
-                 _p(bn.mi), _p(bn.dgamma), _p(bn.dbeta), _p(bn.coef), bn.C, st)
-        _nl.call("drn_bn_bwd_apply", _p(dm), _p(y), _p(bn.coef), _p(addend), _p(out), count, bn.C, st)
+        _nl.call("drn_bn_bwd_finalize_apply", _p(dm), _p(y), _p(bn.bstats), bn.bstats.stride(0), count,
+                 _p(bn.gamma), _p(bn.mi), _p(bn.dgamma), _p(bn.dbeta), _p(addend), _p(out), bn.C, st)
 
     def _block_bwd(self, b: dict, g_i: int, g):
         """g: gradient w.r.t. the block output (scratch[g_i]); returns (index, tensor) of the

@@ -115,6 +115,17 @@ int drn_bn_inference_params(const float* gamma, const float* beta, const float* 
 /* out = [relu](y*scale + shift [+ addend]) over an [M][C] bf16 tensor */
 int drn_bn_apply(const void* y, const void* scale_shift, const void* addend, void* out, long long M,
                  int C, int relu, void* stream);
+/* drn_bn_finalize + drn_bn_apply in ONE launch (every thread derives scale/shift for its own 8
+ * channels; block 0 publishes scale_shift / mean_invstd / moving averages). count = M. */
+int drn_bn_finalize_apply(const void* y, const float* stats, int stats_ld, long long count,
+                          const float* gamma, const float* beta, float* run_mean, float* run_var,
+                          float decay, float eps, void* scale_shift, void* mean_invstd, void* out,
+                          int C, int relu, void* stream);
+/* drn_bn_bwd_finalize + drn_bn_bwd_apply in ONE launch */
+int drn_bn_bwd_finalize_apply(const void* dm, const void* y, const float* stats, int stats_ld,
+                              long long count, const float* gamma, const void* mean_invstd,
+                              float* dgamma, float* dbeta, const void* addend, void* dy, int C,
+                              void* stream);
 int drn_bn_stats(const void* y, float* stats, int stats_ld, long long M, int C, void* stream);
 /* dm = (da [+ addend]) * [y*scale+shift > 0]; stats += (sum dm, sum dm*y).
  * addend_kind: 0 none, 1 same shape, 2 compact stride-2 tensor [N,Ha,Wa,C] added at even pixels,
@@ -156,6 +167,11 @@ int drn_sgd_momentum(float* master, float* grad, float* mom, void* shadow_bf16, 
 /* w_dgrad[c][R-1-r][S-1-s][k] = w_krsc[k][r][s][c] (bf16) */
 int drn_weight_prep_dgrad(const void* w_krsc, void* w_dgrad, int K, int R, int S, int C,
                           void* stream);
+/* the same for many layers in one launch; table = device array of {int64 src_off, int64 dst_off,
+ * int32 K, RS, C, tile_begin} (offsets in elements; tile_begin = running sum of
+ * RS*ceil(K/32)*ceil(C/32)), total_tiles = grand total */
+int drn_weight_prep_dgrad_batched(const void* w_arena, void* dgrad_arena, const void* table,
+                                  int n_layers, int total_tiles, void* stream);
 /* out[n, p*stride, q*stride, :] = dy[n, p, q, :], zero elsewhere; out is [N,U,V,C] */
 int drn_upsample_zero(const void* dy, void* out, int N, int P, int Q, int U, int V, int C,
                       int stride, void* stream);
