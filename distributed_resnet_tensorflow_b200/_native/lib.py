@@ -170,6 +170,9 @@ def stop_call_profile():
     return sorted(((n, c, t) for n, (c, t) in agg.items()), key=lambda r: -r[2])
 
 
+_NVTX = os.environ.get("DRN_NVTX", "0") == "1"
+
+
 def call(name: str, *args) -> None:
     global _launch_count
     _launch_count += 1
@@ -186,4 +189,13 @@ def call(name: str, *args) -> None:
     fn = getattr(lib, name, None)
     if fn is None:
         raise NativeLibraryError(f"symbol {name} missing from {LIB_PATH} (stale build?)")
+    if _NVTX:
+        # DRN_NVTX=1: one NVTX range per native call, so timeline tools show the engine's structure
+        import torch
+        torch.cuda.nvtx.range_push(name)
+        try:
+            check(fn(*args), name)
+        finally:
+            torch.cuda.nvtx.range_pop()
+        return
     check(fn(*args), name)

@@ -52,6 +52,30 @@ def main():
         if rank == 0:
             print(f"allreduce multicast={use_mc} provider={red.grad_buf.provider} maxerr={err:.2e}", flush=True)
 
+    # ---------------- race stress: many back-to-back reductions with random skew between ranks ----
+    # ("race stress ... with random stream delays").  Inputs are small integers so the
+    # expected mean is exact in fp32; any torn read, missed flag or early overwrite shows up as a
+    # non-zero error.  Consecutive calls reuse the same buffer and the same signal pads, which is the
+    # situation the 0<->1 flag protocol has to survive inside a replayed CUDA graph.
+    iters = int(os.environ.get("DRN_STRESS_ITERS", "2000"))
+    rng = np.random.default_rng(1234 + rank)
+    worst = torch.zeros((), device=dev)
+    ramp = (torch.arange(n, device=dev) % 13).float()
+    stream = torch.cuda.current_stream().cuda_stream
+    for it in range(iters):
+        if rng.random() < 0.5:
+            torch.cuda._sleep(int(rng.integers(1, 300000)))   # up to ~150 us of skew on this rank only
+        store["grad"].copy_(ramp * (rank + 1) + float(it % 97))
+        use_mc = bool(red.grad_buf.multicast_ptr) and (it % 2 == 1)
+        nl.call("drn_allreduce_f32", red.grad_buf.ptr_array(), red.grad_buf.mc() if use_mc else 0,
+                red.pads.ptr_array(), rank, world, 0, n, 1.0 / world, 8 + 8 * (it % 3), CH_ALLREDUCE, stream)
+        expect = ramp * ((world + 1) / 2.0) + float(it % 97)
+        worst = torch.maximum(worst, (store["grad"] - expect).abs().max())
+    torch.cuda.synchronize(); dist.barrier()
+    assert float(worst) == 0.0, ("allreduce stress", float(worst))
+    if rank == 0:
+        print(f"allreduce stress: {iters} skewed back-to-back reductions exact", flush=True)
+
     # ---------------- broadcast of the chief's variables (C3) ------------------------------------
     from distributed_resnet_tensorflow_b200.models.init import init_variables as _iv
     from distributed_resnet_tensorflow_b200.models.spec import build_spec as _bs
