@@ -240,13 +240,14 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
   const int units = p.col_tiles * p.co_tiles;
   int splits = split_k;
   if (splits <= 0) {
-    // ~2 waves of CTAs, but keep at least 8 chunks (512 pixels) per CTA
-    // measured on B200 (bench/sweep_wgrad.sh): 1x1 layers are bound by the fp32 red.global traffic
-    // (splits x weights), one wave of CTAs is best; 3x3 layers are bound by L2->SM im2col traffic
-    // and balance better with two waves.
+    // keep at least 8 chunks (512 pixels) per CTA
+    // measured on B200 (bench/sweep_wgrad2.sh): one round of CTAs is best for every ResNet shape -
+    // fewer split-K partial tiles to reduce with red.global and no second pipeline fill.
     static const int waves_env = getenv("DRN_WGRAD_WAVES") ? atoi(getenv("DRN_WGRAD_WAVES")) : 0;
-    const int waves = waves_env > 0 ? waves_env : (d.R * d.S > 1 ? 2 : 1);
-    splits = (waves * num_sms() + units - 1) / units;
+    const int waves = waves_env > 0 ? waves_env : 1;
+    // round DOWN: one CTA per SM is resident (192 KB of stages), so a grid of waves*SMs + a few
+    // CTAs costs a whole extra round
+    splits = (waves * num_sms()) / units;
     int max_splits = p.chunks_total / 8;
     if (max_splits < 1) max_splits = 1;
     if (splits > max_splits) splits = max_splits;

@@ -76,6 +76,61 @@ __global__ void maxpool_fwd_kernel(const BF8* __restrict__ x, BF8* __restrict__ 
   }
 }
 
+// 3x3 / stride 2 specialisation (the only pooling the networks use): the nine loads are issued
+// together (out-of-range taps read a clamped address and are masked afterwards) so that each thread
+// has 144 bytes in flight instead of 16.
+__global__ void maxpool3x3s2_fwd_kernel(const BF8* __restrict__ x, BF8* __restrict__ out,
+                                        U8x8* __restrict__ argmax, int N, int H, int W, int c8, int P,
+                                        int Q, int pad_lo) {
+  const long long total = (long long)N * P * Q * c8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c8);
+    long long t = i / c8;
+    const int q = (int)(t % Q);
+    t /= Q;
+    const int p = (int)(t % P);
+    const long long n = t / P;
+    const int h0 = p * 2 - pad_lo, w0 = q * 2 - pad_lo;
+    BF8 v[9];
+    bool ok[9];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int h = h0 + r, w = w0 + s;
+        ok[r * 3 + s] = h >= 0 && h < H && w >= 0 && w < W;
+        const int hc = min(max(h, 0), H - 1), wc = min(max(w, 0), W - 1);
+        v[r * 3 + s] = x[((n * H + hc) * W + wc) * c8 + cg];
+      }
+    }
+    float best[8];
+    uint32_t arg[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      best[k] = -INFINITY;
+      arg[k] = 0xff;
+    }
+#pragma unroll
+    for (int j = 0; j < 9; ++j) {
+      float f[8];
+      unpack8(v[j], f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (ok[j] && f[k] > best[k]) {
+          best[k] = f[k];
+          arg[k] = j;
+        }
+      }
+    }
+    out[i] = pack8(best);
+    U8x8 a;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a.v[k] = (uint8_t)arg[k];
+    argmax[i] = a;
+  }
+}
+
 // gather formulation: each input pixel sums the gradients of the windows that chose it
 __global__ void maxpool_bwd_kernel(const BF8* __restrict__ dy, const U8x8* __restrict__ argmax,
                                    BF8* __restrict__ dx, int N, int H, int W, int c8, int P, int Q,
@@ -115,6 +170,60 @@ __global__ void maxpool_bwd_kernel(const BF8* __restrict__ dy, const U8x8* __res
       }
     }
     dx[i] = pack8(g);
+  }
+}
+
+// 3x3 / stride 2 specialisation: one thread per 2x2 input patch and 8 channels.  The patch
+// (rows 2i-pad+{0,1}, columns 2j-pad+{0,1}) is touched by exactly the four windows (i|i-1, j|j-1),
+// so each window's gradient and arg-max are loaded once per patch instead of once per pixel.
+__global__ void maxpool3x3s2_bwd_kernel(const BF8* __restrict__ dy, const U8x8* __restrict__ argmax,
+                                        BF8* __restrict__ dx, int N, int H, int W, int c8, int P,
+                                        int Q, int pad_lo, int PI, int QI) {
+  const long long total = (long long)N * PI * QI * c8;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(idx % c8);
+    long long t = idx / c8;
+    const int j = (int)(t % QI);
+    t /= QI;
+    const int i = (int)(t % PI);
+    const long long n = t / PI;
+    float g[4][8];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[a][k] = 0.f;
+    // window (i - di, j - dj) reaches the patch through taps r in {2*di + (0|1)}, s likewise
+#pragma unroll
+    for (int di = 0; di < 2; ++di) {
+#pragma unroll
+      for (int dj = 0; dj < 2; ++dj) {
+        const int p = i - di, q = j - dj;
+        if (p < 0 || p >= P || q < 0 || q >= Q) continue;
+        const long long o = ((n * P + p) * Q + q) * c8 + cg;
+        const U8x8 a = argmax[o];
+        float d[8];
+        unpack8(dy[o], d);
+#pragma unroll
+        for (int er = 0; er < 2 - di; ++er) {
+#pragma unroll
+          for (int es = 0; es < 2 - dj; ++es) {
+            const uint8_t me = (uint8_t)((2 * di + er) * 3 + (2 * dj + es));
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              if (a.v[k] == me) g[er * 2 + es][k] += d[k];
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int er = 0; er < 2; ++er) {
+#pragma unroll
+      for (int es = 0; es < 2; ++es) {
+        const int h = 2 * i - pad_lo + er, w = 2 * j - pad_lo + es;
+        if (h >= 0 && h < H && w >= 0 && w < W) dx[((n * H + h) * W + w) * c8 + cg] = pack8(g[er * 2 + es]);
+      }
+    }
   }
 }
 
@@ -171,8 +280,12 @@ extern "C" int drn_maxpool_fwd(const void* x, void* out, void* argmax, int N, in
   DRN_REQUIRE(C % 8 == 0, "maxpool: C must be a multiple of 8");
   DRN_REQUIRE(ksize * ksize < 255, "maxpool: window too large");
   const long long total = (long long)N * P * Q * (C / 8);
-  maxpool_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
-      (const BF8*)x, (BF8*)out, (U8x8*)argmax, N, H, W, C / 8, P, Q, ksize, stride, pad_lo);
+  if (ksize == 3 && stride == 2)
+    maxpool3x3s2_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+        (const BF8*)x, (BF8*)out, (U8x8*)argmax, N, H, W, C / 8, P, Q, pad_lo);
+  else
+    maxpool_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+        (const BF8*)x, (BF8*)out, (U8x8*)argmax, N, H, W, C / 8, P, Q, ksize, stride, pad_lo);
   DRN_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -181,6 +294,14 @@ extern "C" int drn_maxpool_bwd(const void* dy, const void* argmax, void* dx, int
                                int C, int ksize, int stride, int pad_lo, int P, int Q,
                                void* stream) {
   DRN_REQUIRE(C % 8 == 0, "maxpool: C must be a multiple of 8");
+  if (ksize == 3 && stride == 2 && pad_lo >= 0 && pad_lo <= 1) {
+    const int PI = (H - 1 + pad_lo) / 2 + 1, QI = (W - 1 + pad_lo) / 2 + 1;
+    const long long patches = (long long)N * PI * QI * (C / 8);
+    maxpool3x3s2_bwd_kernel<<<grid_for(patches), 256, 0, (cudaStream_t)stream>>>(
+        (const BF8*)dy, (const U8x8*)argmax, (BF8*)dx, N, H, W, C / 8, P, Q, pad_lo, PI, QI);
+    DRN_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   const long long total = (long long)N * H * W * (C / 8);
   maxpool_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
       (const BF8*)dy, (const U8x8*)argmax, (BF8*)dx, N, H, W, C / 8, P, Q, ksize, stride, pad_lo);

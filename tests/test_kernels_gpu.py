@@ -121,21 +121,24 @@ def test_bn_inference_params():
     assert torch.allclose(ss[:, 0], sc, rtol=1e-5) and torch.allclose(ss[:, 1], b - rm * sc, rtol=1e-4, atol=1e-5)
 
 
-def test_maxpool_same_padding_fwd_bwd():
+@pytest.mark.parametrize("H", [16, 15, 7])
+def test_maxpool_same_padding_fwd_bwd(H):
     nl = _nl()
-    N, H, C = 3, 16, 64
+    N, C = 3, 64
     P = (H + 1) // 2
+    total_pad = max((P - 1) * 2 + 3 - H, 0)
+    lo, hi = total_pad // 2, total_pad - total_pad // 2          # TF "SAME": the extra pixel goes after
     gen = torch.Generator(device="cuda").manual_seed(3)
     x = torch.randn((N, H, H, C), device="cuda", generator=gen).bfloat16()
     out = torch.empty((N, P, P, C), dtype=torch.bfloat16, device="cuda")
     arg = torch.empty((N, P, P, C), dtype=torch.uint8, device="cuda")
-    nl.call("drn_maxpool_fwd", _p(x), _p(out), _p(arg), N, H, H, C, 3, 2, 0, P, P, _st())
+    nl.call("drn_maxpool_fwd", _p(x), _p(out), _p(arg), N, H, H, C, 3, 2, lo, P, P, _st())
     xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
-    ref = F.max_pool2d(F.pad(xr, (0, 1, 0, 1), value=float("-inf")), 3, 2)   # SAME: pad after only
+    ref = F.max_pool2d(F.pad(xr, (lo, hi, lo, hi), value=float("-inf")), 3, 2)
     assert torch.equal(out.float(), ref.permute(0, 2, 3, 1))
     dy = torch.randn((N, P, P, C), device="cuda", generator=gen).bfloat16()
-    dx = torch.empty_like(x)
-    nl.call("drn_maxpool_bwd", _p(dy), _p(arg), _p(dx), N, H, H, C, 3, 2, 0, P, P, _st())
+    dx = torch.full_like(x, float("nan"))                        # every pixel must be written
+    nl.call("drn_maxpool_bwd", _p(dy), _p(arg), _p(dx), N, H, H, C, 3, 2, lo, P, P, _st())
     ref.backward(dy.float().permute(0, 3, 1, 2))
     assert (dx.float() - xr.grad.permute(0, 2, 3, 1)).abs().max() < 0.02
 
