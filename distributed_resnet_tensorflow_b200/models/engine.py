@@ -20,6 +20,7 @@ from __future__ import annotations
 
 import ctypes
 import math
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
@@ -32,6 +33,8 @@ from ..ops.conv import ConvGeom
 from .spec import BlockSpec, BNSpec, ConvSpec, NetSpec
 
 BN_DECAY = 0.997
+# filter gradients on a second stream (DRN_WGRAD_STREAM=0 keeps everything on one stream)
+WGRAD_SIDE_STREAM = os.environ.get("DRN_WGRAD_STREAM", "1") != "0"
 BN_EPS = 1e-5
 VGG_MEANS = (123.68 / 255.0, 116.78 / 255.0, 103.94 / 255.0)  # vgg_preprocessing.py:37-39 (in [0,1] units)
 
@@ -325,7 +328,15 @@ class NativeResNet:
         self.d_pooled = torch.empty((B, s.dense_in), dtype=torch.bfloat16, device=self.device)
         # backward scratch: a few buffers of the largest activation size
         max_elems = max([self.y_stem.numel()] + [b["max_elems"] for b in self.blocks])
-        self._scratch = [torch.empty(max_elems, dtype=torch.bfloat16, device=self.device) for _ in range(6)]
+        n_scratch = 6 + (4 if WGRAD_SIDE_STREAM else 0)   # longer reuse distance under overlap
+        self._scratch = [torch.empty(max_elems, dtype=torch.bfloat16, device=self.device) for _ in range(n_scratch)]
+        # filter gradients have no consumer before the optimizer, so they run on a second,
+        # lower-priority stream and fill the SMs the persistent data-gradient kernels leave idle in
+        # their last round of tiles (1 CTA/SM kernels, 196 tiles on 148 SMs in stage 3, ...)
+        self._wg_stream = torch.cuda.Stream(device=self.device, priority=0) if WGRAD_SIDE_STREAM else None
+        self._wg_last = None
+        self._buf_event = {}
+        self._ev_pool, self._ev_next = [], 0
 
     def _plan_block(self, blk: BlockSpec) -> dict:
         B = self.B
@@ -450,8 +461,39 @@ class NativeResNet:
                  _p(self.stem.w), _p(self.y_stem), 0, _p(stats), stats.stride(0) if stats is not None else 0,
                  0, EPI_PLAIN, 0, self._st())
 
-    def _wgrad(self, conv: _Conv, x, dy):
-        _nl.call("drn_conv_wgrad", ctypes.byref(conv.desc), _p(x), _p(dy), _p(conv.dw), 0, self._st())
+    def _event(self):
+        if self._ev_next == len(self._ev_pool):
+            self._ev_pool.append(torch.cuda.Event())
+        ev = self._ev_pool[self._ev_next]
+        self._ev_next += 1
+        return ev
+
+    def _on_wgrad_stream(self, launch, dy_idx: Optional[int]) -> None:
+        """Run ``launch(stream_handle)`` after everything issued so far on the current stream, on the
+        filter-gradient stream; remember which scratch buffer it reads so that _get() can order the
+        next writer of that buffer behind it."""
+        side = self._wg_stream
+        if side is None:
+            launch(self._st())
+            return
+        ready = self._event()
+        ready.record(torch.cuda.current_stream())
+        side.wait_event(ready)
+        launch(side.cuda_stream)
+        done = self._event()
+        done.record(side)
+        self._wg_last = done
+        if dy_idx is not None:
+            self._buf_event[dy_idx] = done
+
+    def _join_wgrads(self) -> None:
+        if self._wg_last is not None:
+            torch.cuda.current_stream().wait_event(self._wg_last)
+            self._wg_last = None
+
+    def _wgrad(self, conv: _Conv, x, dy, dy_idx: Optional[int] = None):
+        self._on_wgrad_stream(lambda st: _nl.call("drn_conv_wgrad", ctypes.byref(conv.desc), _p(x), _p(dy),
+                                                  _p(conv.dw), 0, st), dy_idx)
 
     def _bn_finalize(self, bn: _BN, count: int, training: bool):
         st = self._st()
@@ -553,8 +595,15 @@ class NativeResNet:
     # ---- backward -----------------------------------------------------------------------------
     def _get(self, like):
         """Borrow a scratch buffer shaped like ``like`` (stream order makes reuse safe)."""
-        i = self._free.pop()
+        i = self._pop_free()
         return i, self._scratch[i][: like.numel()].view(like.shape)
+
+    def _pop_free(self) -> int:
+        i = self._free.pop(0)            # FIFO: the buffer released longest ago
+        ev = self._buf_event.pop(i, None)
+        if ev is not None:               # a filter-gradient launch may still be reading it
+            torch.cuda.current_stream().wait_event(ev)
+        return i
 
     def _put(self, i: int) -> None:
         self._free.append(i)
@@ -595,10 +644,12 @@ class NativeResNet:
         st = self._st()
         marks = self.range_marks()
         self._free = list(range(len(self._scratch)))
+        self._buf_event.clear()
+        self._ev_next = 0
         # dense
         self._conv(self.dense_ddesc, self.dlogits, self.dense_wd, self.d_pooled)
-        _nl.call("drn_conv_wgrad", ctypes.byref(self.dense_desc), _p(self.pooled), _p(self.dlogits),
-                 _p(self.dense_dw), 0, st)
+        self._on_wgrad_stream(lambda h: _nl.call("drn_conv_wgrad", ctypes.byref(self.dense_desc), _p(self.pooled),
+                                                 _p(self.dlogits), _p(self.dense_dw), 0, h), None)
         # final BN + ReLU + average pool
         fb = self.final_bn
         x = self.x_final
@@ -610,10 +661,12 @@ class NativeResNet:
         self._bn_bwd(fb, dm, x, None, g)
         self._put(dm_i)
         if range_hook is not None:
+            self._join_wgrads()
             range_hook(marks[-2], marks[-1], False)
         for bi in range(len(self.blocks) - 1, -1, -1):
             g_i, g = self._block_bwd(self.blocks[bi], g_i, g)
             if range_hook is not None:
+                self._join_wgrads()
                 range_hook(marks[bi + 1], marks[bi + 2], False)
         # stem
         if s.maxpool:
@@ -625,11 +678,13 @@ class NativeResNet:
             self._put(g_i)
             g_i, g = d_i, d_stem
         if self.stem_view is not None:
-            _nl.call("drn_conv_wgrad_view", ctypes.byref(self.stem.desc), ctypes.byref(self.stem_view),
-                     _p(self.x0), _p(g), _p(self.stem.dw), 0, st)
+            self._on_wgrad_stream(lambda h: _nl.call("drn_conv_wgrad_view", ctypes.byref(self.stem.desc),
+                                                     ctypes.byref(self.stem_view), _p(self.x0), _p(g),
+                                                     _p(self.stem.dw), 0, h), g_i)
         else:
-            self._wgrad(self.stem, self.x0, g)
+            self._wgrad(self.stem, self.x0, g, g_i)
         self._put(g_i)
+        self._join_wgrads()
         if self.stem_mask is not None:
             _nl.call("drn_mul_inplace_f32", _p(self.stem.dw), _p(self.stem_mask),
                      self.stem_mask.numel(), st)
@@ -652,7 +707,7 @@ class NativeResNet:
         for i in range(len(convs) - 1, 0, -1):
             c, bn = convs[i], bns[i - 1]
             y_prev, a_prev = ys[i - 1], acts[i - 1]
-            self._wgrad(c, a_prev, dy)
+            self._wgrad(c, a_prev, dy, dy_i)
             dm_i, dm = self._get(y_prev)
             self._dgrad(c, dy, dm, side=y_prev, stats=bn.bstats, ss=bn.ss, mode=EPI_BNBWD)
             if dy_i != g_i:
@@ -662,11 +717,11 @@ class NativeResNet:
             self._put(dm_i)
             dy_i, dy = n_i, ndy
         c0 = convs[0]
-        self._wgrad(c0, a0, dy)
+        self._wgrad(c0, a0, dy, dy_i)
         Bn, H, W, C = x.shape
         if "proj" in b:
             pj = b["proj"]
-            self._wgrad(pj, a0, g)
+            self._wgrad(pj, a0, g, g_i)
             da_i, da = self._get(x)
             self._dgrad(c0, dy, da)
             if dy_i != g_i:
@@ -679,7 +734,7 @@ class NativeResNet:
                          _p(bn0.ss), _p(dm), _p(bn0.bstats), bn0.bstats.stride(0), C, st)
             else:
                 # compact data gradient of the 1x1/stride-s projection: a 1x1/1 conv over g
-                t_i = self._free.pop()
+                t_i = self._pop_free()
                 t = self._scratch[t_i][: Bn * pj.g.P * pj.g.Q * C].view(Bn, pj.g.P, pj.g.Q, C)
                 self._conv(b["proj_cdesc"], g, pj.wd, t)
                 _nl.call("drn_bn_bwd_mask_reduce", _p(da), _p(t), 2, Bn, H, W, pj.g.P, pj.g.Q, 0.0,

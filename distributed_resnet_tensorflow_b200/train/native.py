@@ -179,7 +179,9 @@ class NativeTrainer:
         self._restore(snapshot)
         g = torch.cuda.CUDAGraph()
         before = _nl.launch_count()
-        with torch.cuda.graph(g):
+        # capture on a high-priority stream: kernel nodes inherit it, so the dependent chain wins the
+        # SMs over the filter-gradient branch (engine._wg_stream, lowest priority)
+        with torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.device, priority=-1)):
             self._step_body()
         self._launches_in_graph = _nl.launch_count() - before
         torch.cuda.synchronize(self.device)
@@ -193,9 +195,13 @@ class NativeTrainer:
         self._step_body()                      # warm
         torch.cuda.synchronize(self.device)
         self._restore(snap)
+        side, self.engine._wg_stream = self.engine._wg_stream, None   # one stream: events bracket every launch
         _nl.start_call_profile()
-        self._step_body()
-        rows = _nl.stop_call_profile()
+        try:
+            self._step_body()
+        finally:
+            rows = _nl.stop_call_profile()
+            self.engine._wg_stream = side
         self._restore(snap)
         total = sum(r[2] for r in rows) or 1.0
         lines = [f"{'entry point':28s} {'calls':>6s} {'total us':>10s} {'share':>7s}"]
