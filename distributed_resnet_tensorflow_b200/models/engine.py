@@ -442,12 +442,14 @@ class NativeResNet:
         self._prep_table = torch.from_numpy(tab.view(np.uint8).copy()).to(self.device)
         self._prep_layers, self._prep_tiles = len(rows), tiles
 
-    def prep_dgrad_weights(self) -> None:
-        """Flipped + transposed bf16 banks of every layer that has a data gradient (one launch)."""
+    def prep_dgrad_weights(self, stream_handle: Optional[int] = None) -> None:
+        """Flipped + transposed bf16 banks of every layer that has a data gradient (one launch).
+        forward(training=True) issues it on the filter-gradient stream, under the forward pass;
+        backward() waits for it."""
         if not hasattr(self, "_prep_table"):
             self._build_prep_table()
         _nl.call("drn_weight_prep_dgrad_batched", _p(self.shadow), _p(self._wd_arena), _p(self._prep_table),
-                 self._prep_layers, self._prep_tiles, self._st())
+                 self._prep_layers, self._prep_tiles, self._st() if stream_handle is None else stream_handle)
 
     def _conv(self, desc, x, w, y, side=None, stats=None, ss=None, mode=EPI_PLAIN):
         _nl.call("drn_conv_igemm", ctypes.byref(desc), _p(x), _p(w), _p(y), _p(side), _p(stats),
@@ -536,6 +538,8 @@ class NativeResNet:
         st = self._st()
         if training:
             self._stats_arena.zero_()
+            self._ev_next = 0
+            self._on_wgrad_stream(self.prep_dgrad_weights, None)
         first_bn = self.blocks[0]["bn0"]
         if s.maxpool:
             self._stem_conv(None)
@@ -645,7 +649,7 @@ class NativeResNet:
         marks = self.range_marks()
         self._free = list(range(len(self._scratch)))
         self._buf_event.clear()
-        self._ev_next = 0
+        self._join_wgrads()          # the dgrad filter banks refreshed under forward()
         # dense
         self._conv(self.dense_ddesc, self.dlogits, self.dense_wd, self.d_pooled)
         self._on_wgrad_stream(lambda h: _nl.call("drn_conv_wgrad", ctypes.byref(self.dense_desc), _p(self.pooled),
@@ -761,7 +765,6 @@ class NativeResNet:
         st = self._st()
         _nl.call("drn_sgd_momentum", _p(self.master), _p(self.grad), _p(self.mom), _p(self.shadow),
                  self.layout.total, _p(self.hyper), _p(self.scalars[1:]) if want_l2 else 0, 1, st)
-        self.prep_dgrad_weights()
 
     def set_hyper(self, lr: float, momentum: float, weight_decay: float, grad_scale: float = 1.0):
         self.hyper.copy_(torch.tensor([lr, momentum, weight_decay, grad_scale], dtype=torch.float32),

@@ -130,7 +130,6 @@ class AllreduceReducer(_ReducerBase):
 
         self._run_backward(engine, on_bucket)
         cur.wait_stream(cs)
-        engine.prep_dgrad_weights()
 
 
 class ParameterServerReducer(_ReducerBase):
@@ -158,7 +157,6 @@ class ParameterServerReducer(_ReducerBase):
 
         self._run_backward(engine, on_bucket)
         cur.wait_stream(cs)
-        engine.prep_dgrad_weights()
 
     def gather_master(self, engine) -> None:
         """Collect every shard's fp32 master / momentum slices on all ranks (checkpointing): each
