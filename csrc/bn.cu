@@ -11,6 +11,8 @@
 // Numerics follow tf.layers.batch_normalization(fused=True) as used by the reference
 // (resnet_model_official.py:41-50): biased variance to normalise, unbiased variance into the
 // moving average, decay 0.997, eps 1e-5.  Ops K5-K9.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "host.cuh"
 #include "../include/drn_b200.h"
@@ -44,6 +46,8 @@ __global__ void bn_finalize_kernel(const float* __restrict__ stats, int stats_ld
                                    float* __restrict__ run_var, float one_minus_decay, float eps,
                                    float2* __restrict__ scale_shift, float2* __restrict__ mean_invstd,
                                    int C) {
+  pdl_trigger();
+  pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float mean = stats[c] * inv_count;
@@ -65,6 +69,8 @@ __global__ void bn_inference_params_kernel(const float* __restrict__ gamma,
                                            const float* __restrict__ run_mean,
                                            const float* __restrict__ run_var, float eps,
                                            float2* __restrict__ scale_shift, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float sc = gamma[c] * rsqrtf(run_var[c] + eps);
@@ -77,6 +83,8 @@ __global__ void bn_inference_params_kernel(const float* __restrict__ gamma,
 __global__ void bn_apply_kernel(const BF8* __restrict__ y, const float2* __restrict__ scale_shift,
                                 const BF8* __restrict__ addend, BF8* __restrict__ out,
                                 long long n_vec, int c8, int relu) {
+  pdl_trigger();
+  pdl_wait();
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int cg = (int)(i % c8);
@@ -140,6 +148,8 @@ __global__ void bn_apply_kernel(const BF8* __restrict__ y, const float2* __restr
 // per-channel sum and sum of squares of a [M][C] tensor (standalone producer of BN statistics)
 __global__ void bn_stats_kernel(const BF8* __restrict__ y, float* __restrict__ stats, int stats_ld,
                                 long long M, int c8) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float s_acc[kThreads * 16];
   const int cg = threadIdx.x % c8;
   const int pl = threadIdx.x / c8;
@@ -182,6 +192,8 @@ __global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8*
                                           const float2* __restrict__ scale_shift,
                                           BF8* __restrict__ dm, float* __restrict__ stats,
                                           int stats_ld, long long M, int c8) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float s_acc[kThreads * 16];
   const int cg = threadIdx.x % c8;
   const int pl = threadIdx.x / c8;
@@ -258,6 +270,8 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ stats, int stat
                                        const float2* __restrict__ mean_invstd,
                                        float* __restrict__ dgamma, float* __restrict__ dbeta,
                                        float4* __restrict__ coef, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float s1 = stats[c], s2 = stats[stats_ld + c];
@@ -276,6 +290,8 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ stats, int stat
 __global__ void bn_bwd_apply_kernel(const BF8* __restrict__ dm, const BF8* __restrict__ y,
                                     const float4* __restrict__ coef, const BF8* __restrict__ addend,
                                     BF8* __restrict__ dy, long long n_vec, int c8) {
+  pdl_trigger();
+  pdl_wait();
   const long long stride = (long long)gridDim.x * blockDim.x;  // multiple of c8: channels stay fixed
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int cg = (int)(i % c8);
@@ -341,6 +357,8 @@ __global__ void bn_finalize_apply_kernel(const BF8* __restrict__ y, const float*
                                          float one_minus_decay, float eps,
                                          float2* __restrict__ scale_shift, float2* __restrict__ mean_invstd,
                                          BF8* __restrict__ out, long long n_vec, int c8, int relu) {
+  pdl_trigger();
+  pdl_wait();
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int cg = (int)(i % c8);
@@ -392,6 +410,29 @@ __global__ void bn_finalize_apply_kernel(const BF8* __restrict__ y, const float*
   }
 }
 
+template <int POL>
+__device__ __forceinline__ BF8 ld_vec(const BF8* p) {
+  if (POL == 0) return *p;
+  BF8 r;
+  // streaming read: the tensor is dead (or far from its next use) after this kernel
+  asm volatile("ld.global.cs.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3])
+               : "l"(p));
+  return r;
+}
+template <int POL>
+__device__ __forceinline__ void st_vec(BF8* p, const BF8& r) {
+  if (POL == 0) {
+    *p = r;
+    return;
+  }
+  asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(r.v[0]), "r"(r.v[1]),
+               "r"(r.v[2]), "r"(r.v[3])
+               : "memory");
+}
+
+// U vectors in flight per thread; POL = cache policy of the streams (0 default, 1 streaming)
+template <int U, int POL>
 __global__ void bn_bwd_finalize_apply_kernel(const BF8* __restrict__ dm, const BF8* __restrict__ y,
                                              const float* __restrict__ stats, int stats_ld,
                                              float inv_count, const float* __restrict__ gamma,
@@ -399,6 +440,8 @@ __global__ void bn_bwd_finalize_apply_kernel(const BF8* __restrict__ dm, const B
                                              float* __restrict__ dgamma, float* __restrict__ dbeta,
                                              const BF8* __restrict__ addend, BF8* __restrict__ dy,
                                              long long n_vec, int c8) {
+  pdl_trigger();
+  pdl_wait();
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int cg = (int)(i % c8);
@@ -418,35 +461,31 @@ __global__ void bn_bwd_finalize_apply_kernel(const BF8* __restrict__ dm, const B
     cb[k] = -ca[k] * mi.y * dg * inv_count;
     cc[k] = -ca[k] * s1 * inv_count - cb[k] * mi.x;
   }
-  for (; i + stride < n_vec; i += 2 * stride) {
-    const BF8 d0 = dm[i], d1 = dm[i + stride];
-    const BF8 y0 = y[i], y1 = y[i + stride];
-    BF8 a0 = d0, a1 = d1;
-    if (addend != nullptr) {
-      a0 = addend[i];
-      a1 = addend[i + stride];
-    }
-    float g0[8], g1[8], t0[8], t1[8];
-    unpack8(d0, g0);
-    unpack8(d1, g1);
-    unpack8(y0, t0);
-    unpack8(y1, t1);
+  const bool has_add = addend != nullptr;
+  for (; i + (U - 1) * stride < n_vec; i += U * stride) {
+    BF8 d[U], t[U], a[U];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      g0[k] = fmaf(ca[k], g0[k], fmaf(cb[k], t0[k], cc[k]));
-      g1[k] = fmaf(ca[k], g1[k], fmaf(cb[k], t1[k], cc[k]));
-    }
-    if (addend != nullptr) {
-      unpack8(a0, t0);
-      unpack8(a1, t1);
+    for (int u = 0; u < U; ++u) d[u] = ld_vec<POL>(dm + i + u * stride);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        g0[k] += t0[k];
-        g1[k] += t1[k];
+    for (int u = 0; u < U; ++u) t[u] = ld_vec<0>(y + i + u * stride);
+    if (has_add) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) a[u] = ld_vec<POL>(addend + i + u * stride);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float g[8], yy[8];
+      unpack8(d[u], g);
+      unpack8(t[u], yy);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = fmaf(ca[k], g[k], fmaf(cb[k], yy[k], cc[k]));
+      if (has_add) {
+        unpack8(a[u], yy);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] += yy[k];
       }
+      st_vec<POL>(dy + i + u * stride, pack8(g));
     }
-    dy[i] = pack8(g0);
-    dy[i + stride] = pack8(g1);
   }
   for (; i < n_vec; i += stride) {
     float g[8], yy[8];
@@ -454,7 +493,7 @@ __global__ void bn_bwd_finalize_apply_kernel(const BF8* __restrict__ dm, const B
     unpack8(y[i], yy);
 #pragma unroll
     for (int k = 0; k < 8; ++k) g[k] = fmaf(ca[k], g[k], fmaf(cb[k], yy[k], cc[k]));
-    if (addend != nullptr) {
+    if (has_add) {
       float ad[8];
       unpack8(addend[i], ad);
 #pragma unroll
@@ -469,6 +508,21 @@ int check_c(int C, const char* who) {
   if (C % 8 != 0 || c8 > kThreads || (c8 & (c8 - 1)) != 0)
     return fail("%s: C=%d must be 8 * a power of two <= 2048", who, C);
   return 0;
+}
+
+// Grid for the fused finalize+apply kernels: every thread first derives the coefficients of its 8
+// channels (a few dozen dependent loads and flops), so small tensors want FEW threads with several
+// vectors each rather than a full machine of threads with two.
+int fused_grid(long long n_vec) {
+  static const int vpt = getenv("DRN_BN_VPT") ? atoi(getenv("DRN_BN_VPT")) : 8;
+  static const int bps = getenv("DRN_BN_BPS") ? atoi(getenv("DRN_BN_BPS")) : 8;
+  long long blocks = (n_vec + (long long)kThreads * vpt - 1) / ((long long)kThreads * vpt);
+  const long long lo = num_sms(), hi = (long long)num_sms() * bps;
+  if (blocks < lo) blocks = lo;
+  if (blocks > hi) blocks = hi;
+  const long long all = (n_vec + kThreads - 1) / kThreads;
+  if (blocks > all) blocks = all;
+  return (int)(blocks > 0 ? blocks : 1);
 }
 
 int ew_grid(long long n_vec) {
@@ -488,19 +542,17 @@ extern "C" int drn_bn_finalize(const float* stats, int stats_ld, long long count
                                void* stream) {
   DRN_REQUIRE(count > 0, "bn_finalize: count must be positive");
   const float unbias = count > 1 ? (float)((double)count / (double)(count - 1)) : 1.f;
-  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-      stats, stats_ld, (float)(1.0 / (double)count), unbias, gamma, beta, run_mean, run_var,
-      1.f - decay, eps, (float2*)scale_shift, (float2*)mean_invstd, C);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(bn_finalize_kernel, dim3((C + 127) / 128), dim3(128), 0, (cudaStream_t)stream,
+                            stats, stats_ld, (float)(1.0 / (double)count), unbias, gamma, beta, run_mean, run_var,
+      1.f - decay, eps, (float2*)scale_shift, (float2*)mean_invstd, C));
   return 0;
 }
 
 extern "C" int drn_bn_inference_params(const float* gamma, const float* beta, const float* run_mean,
                                        const float* run_var, float eps, void* scale_shift, int C,
                                        void* stream) {
-  bn_inference_params_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-      gamma, beta, run_mean, run_var, eps, (float2*)scale_shift, C);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(bn_inference_params_kernel, dim3((C + 127) / 128), dim3(128), 0, (cudaStream_t)stream,
+                            gamma, beta, run_mean, run_var, eps, (float2*)scale_shift, C));
   return 0;
 }
 
@@ -508,9 +560,8 @@ extern "C" int drn_bn_apply(const void* y, const void* scale_shift, const void* 
                             long long M, int C, int relu, void* stream) {
   if (int e = check_c(C, "bn_apply")) return e;
   const long long n_vec = M * (C / 8);
-  bn_apply_kernel<<<ew_grid(n_vec), kThreads, 0, (cudaStream_t)stream>>>(
-      (const BF8*)y, (const float2*)scale_shift, (const BF8*)addend, (BF8*)out, n_vec, C / 8, relu);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(bn_apply_kernel, dim3(ew_grid(n_vec)), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)y, (const float2*)scale_shift, (const BF8*)addend, (BF8*)out, n_vec, C / 8, relu));
   return 0;
 }
 
@@ -521,9 +572,9 @@ extern "C" int drn_bn_stats(const void* y, float* stats, int stats_ld, long long
   long long blocks = (M + lanes - 1) / lanes;
   const long long cap = (long long)num_sms() * 4;
   if (blocks > cap) blocks = cap;
-  bn_stats_kernel<<<(int)blocks, kThreads, 0, (cudaStream_t)stream>>>((const BF8*)y, stats,
-                                                                      stats_ld, M, C / 8);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(bn_stats_kernel, dim3((int)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)y, stats,
+                                                                      stats_ld, M, C / 8));
   return 0;
 }
 
@@ -540,20 +591,18 @@ extern "C" int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int ad
   long long blocks = (M + lanes - 1) / lanes;
   const long long cap = (long long)num_sms() * 4;
   if (blocks > cap) blocks = cap;
-  bn_bwd_mask_reduce_kernel<<<(int)blocks, kThreads, 0, (cudaStream_t)stream>>>(
-      (const BF8*)da, (const BF8*)addend, addend_kind, H, W, Ha, Wa, bcast_scale, (const BF8*)y,
-      (const float2*)scale_shift, (BF8*)dm, stats, stats_ld, M, C / 8);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(bn_bwd_mask_reduce_kernel, dim3((int)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)da, (const BF8*)addend, addend_kind, H, W, Ha, Wa, bcast_scale, (const BF8*)y,
+      (const float2*)scale_shift, (BF8*)dm, stats, stats_ld, M, C / 8));
   return 0;
 }
 
 extern "C" int drn_bn_bwd_finalize(const float* stats, int stats_ld, long long count,
                                    const float* gamma, const void* mean_invstd, float* dgamma,
                                    float* dbeta, void* coef, int C, void* stream) {
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-      stats, stats_ld, (float)(1.0 / (double)count), gamma, (const float2*)mean_invstd, dgamma,
-      dbeta, (float4*)coef, C);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(bn_bwd_finalize_kernel, dim3((C + 127) / 128), dim3(128), 0, (cudaStream_t)stream,
+                            stats, stats_ld, (float)(1.0 / (double)count), gamma, (const float2*)mean_invstd, dgamma,
+      dbeta, (float4*)coef, C));
   return 0;
 }
 
@@ -561,10 +610,9 @@ extern "C" int drn_bn_bwd_apply(const void* dm, const void* y, const void* coef,
                                 void* dy, long long M, int C, void* stream) {
   if (int e = check_c(C, "bn_bwd_apply")) return e;
   const long long n_vec = M * (C / 8);
-  bn_bwd_apply_kernel<<<ew_grid(n_vec), kThreads, 0, (cudaStream_t)stream>>>(
-      (const BF8*)dm, (const BF8*)y, (const float4*)coef, (const BF8*)addend, (BF8*)dy, n_vec,
-      C / 8);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(bn_bwd_apply_kernel, dim3(ew_grid(n_vec)), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)dm, (const BF8*)y, (const float4*)coef, (const BF8*)addend, (BF8*)dy, n_vec,
+      C / 8));
   return 0;
 }
 
@@ -577,11 +625,10 @@ extern "C" int drn_bn_finalize_apply(const void* y, const float* stats, int stat
   DRN_REQUIRE(count > 0, "bn_finalize_apply: count must be positive");
   const float unbias = count > 1 ? (float)((double)count / (double)(count - 1)) : 1.f;
   const long long n_vec = count * (C / 8);
-  bn_finalize_apply_kernel<<<ew_grid(n_vec), kThreads, 0, (cudaStream_t)stream>>>(
-      (const BF8*)y, stats, stats_ld, (float)(1.0 / (double)count), unbias, gamma, beta, run_mean,
+  DRN_CHECK_CUDA(launch_pdl(bn_finalize_apply_kernel, dim3(fused_grid(n_vec)), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)y, stats, stats_ld, (float)(1.0 / (double)count), unbias, gamma, beta, run_mean,
       run_var, 1.f - decay, eps, (float2*)scale_shift, (float2*)mean_invstd, (BF8*)out, n_vec, C / 8,
-      relu);
-  DRN_CHECK_CUDA(cudaGetLastError());
+      relu));
   return 0;
 }
 
@@ -592,9 +639,15 @@ extern "C" int drn_bn_bwd_finalize_apply(const void* dm, const void* y, const fl
                                          const void* addend, void* dy, int C, void* stream) {
   if (int e = check_c(C, "bn_bwd_finalize_apply")) return e;
   const long long n_vec = count * (C / 8);
-  bn_bwd_finalize_apply_kernel<<<ew_grid(n_vec), kThreads, 0, (cudaStream_t)stream>>>(
-      (const BF8*)dm, (const BF8*)y, stats, stats_ld, (float)(1.0 / (double)count), gamma,
-      (const float2*)mean_invstd, dgamma, dbeta, (const BF8*)addend, (BF8*)dy, n_vec, C / 8);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  static const int variant = getenv("DRN_BN_VARIANT") ? atoi(getenv("DRN_BN_VARIANT")) : 0;
+  const int blocks = fused_grid(n_vec);
+  auto kern = variant == 1   ? bn_bwd_finalize_apply_kernel<2, 1>
+              : variant == 2 ? bn_bwd_finalize_apply_kernel<4, 0>
+              : variant == 3 ? bn_bwd_finalize_apply_kernel<4, 1>
+              : variant == 4 ? bn_bwd_finalize_apply_kernel<1, 0>
+                             : bn_bwd_finalize_apply_kernel<2, 0>;
+  DRN_CHECK_CUDA(launch_pdl(kern, dim3((unsigned)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)dm, (const BF8*)y, stats, stats_ld, (float)(1.0 / (double)count), gamma,
+                            (const float2*)mean_invstd, dgamma, dbeta, (const BF8*)addend, (BF8*)dy, n_vec, C / 8));
   return 0;
 }

@@ -35,6 +35,13 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// Programmatic dependent launch (host side: launch_pdl in host.cuh).  pdl_trigger() lets the next
+// kernel in the stream be scheduled as soon as every CTA of this grid has executed it or exited;
+// pdl_wait() blocks until all predecessor grids have completed and their writes are visible.
+// Both are no-ops when the kernel was launched without the attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(

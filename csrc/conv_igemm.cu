@@ -118,6 +118,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_trigger();
 
   // Each CTA owns a contiguous range of the n-major tile order, so it crosses a column-tile
   // boundary (statistics flush, scale/shift reload) at most once or twice.
@@ -151,6 +152,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
+  // everything above (barriers, TMEM, descriptor prefetch) overlapped the previous kernel's tail
+  pdl_wait();
 
   if (warp == 0) {
     // ======================= TMA producer =======================
@@ -542,8 +545,8 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
     attr_set = true;
   }
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
-  conv_igemm_kernel<KC, BN><<<grid, kNumThreads, smem_bytes, stream>>>(tA, tB, tC, tR, p);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN>, dim3(grid), dim3(kNumThreads), smem_bytes, stream,
+                            tA, tB, tC, tR, p));
   return 0;
 }
 

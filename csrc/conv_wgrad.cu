@@ -84,6 +84,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_trigger();
 
   // decode the work unit
   int u = blockIdx.x;
@@ -118,6 +119,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
+  pdl_wait();
 
   if (n_chunks > 0) {
     if (warp == 0) {
@@ -247,7 +249,8 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
     const int waves = waves_env > 0 ? waves_env : 1;
     // round DOWN: one CTA per SM is resident (192 KB of stages), so a grid of waves*SMs + a few
     // CTAs costs a whole extra round
-    splits = (waves * num_sms()) / units;
+    static const int sms_env = getenv("DRN_WGRAD_SMS") ? atoi(getenv("DRN_WGRAD_SMS")) : 0;
+    splits = (waves * (sms_env > 0 ? sms_env : num_sms())) / units;
     int max_splits = p.chunks_total / 8;
     if (max_splits < 1) max_splits = 1;
     if (splits > max_splits) splits = max_splits;
@@ -284,8 +287,8 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
     attr_set = true;
   }
   const int grid = units * splits;
-  conv_wgrad_kernel<CWA, CWB><<<grid, kThreads, C_::kSmemBytes, stream>>>(tDY, tX, p);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl_conv(conv_wgrad_kernel<CWA, CWB>, dim3(grid), dim3(kThreads), C_::kSmemBytes, stream,
+                            tDY, tX, p));
   return 0;
 }
 

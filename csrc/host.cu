@@ -1,6 +1,7 @@
 #include "host.cuh"
 
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -26,6 +27,14 @@ int fail(const char* fmt, ...) {
 const ConvView*& current_view() {
   static thread_local const ConvView* v = nullptr;
   return v;
+}
+
+int pdl_mask() {
+  static const int m = []() {
+    const char* e = getenv("DRN_PDL");
+    return e != nullptr ? atoi(e) : 0;   // measured: no gain next to the two-stream overlap
+  }();
+  return m;
 }
 
 int num_sms() {

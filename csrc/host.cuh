@@ -34,6 +34,29 @@ int fail(const char* fmt, ...);
 
 int num_sms();
 
+// Programmatic dependent launch: the kernel may be scheduled while its predecessor in the stream is
+// still draining; it must execute pdl_wait() (common.cuh) before touching memory the predecessor
+// produced.  Inside a captured graph this becomes a programmatic edge.  DRN_PDL=0 turns it off.
+int pdl_mask();   // bit 0: element-wise / pooling / optimizer kernels, bit 1: tcgen05 convolution kernels
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl_kind(int kind_bit, void (*kernel)(KArgs...), dim3 grid, dim3 block,
+                                   size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (pdl_mask() & kind_bit) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#define launch_pdl(...) launch_pdl_kind(1, __VA_ARGS__)
+#define launch_pdl_conv(...) launch_pdl_kind(2, __VA_ARGS__)
+
 enum SwizzleMode { SWZ_NONE = 0, SWZ_32 = 32, SWZ_64 = 64, SWZ_128 = 128 };
 
 // 2-D tiled map over a row-major [rows][cols] matrix of 2- or 4-byte elements.

@@ -34,6 +34,8 @@ __global__ void softmax_xent_kernel(const __nv_bfloat16* __restrict__ logits, in
                                     int classes, float grad_scale, __nv_bfloat16* __restrict__ dlogits,
                                     float* __restrict__ dbias, float* __restrict__ probs,
                                     float* __restrict__ loss_sum, int* __restrict__ correct) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float s_red[kThreads / 32];
   __shared__ int s_arg[kThreads / 32];
   const int row = blockIdx.x;
@@ -99,9 +101,8 @@ extern "C" int drn_softmax_xent(const void* logits, int ld, const float* bias, c
                                 int B, int classes, float grad_scale, void* dlogits, float* dbias,
                                 float* probs, float* loss_sum, int* correct, void* stream) {
   DRN_REQUIRE(classes <= ld, "softmax_xent: classes (%d) > ld (%d)", classes, ld);
-  softmax_xent_kernel<<<B, kThreads, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)logits, ld, bias, labels, classes, grad_scale, (__nv_bfloat16*)dlogits,
-      dbias, probs, loss_sum, correct);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(softmax_xent_kernel, dim3(B), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const __nv_bfloat16*)logits, ld, bias, labels, classes, grad_scale, (__nv_bfloat16*)dlogits,
+      dbias, probs, loss_sum, correct));
   return 0;
 }

@@ -21,6 +21,8 @@ __global__ void sgd_momentum_kernel(float4* __restrict__ w, float4* __restrict__
                                     float4* __restrict__ m, uint2* __restrict__ shadow,
                                     long long n4, const float* __restrict__ hyper,
                                     float* __restrict__ l2_sum, int zero_grad) {
+  pdl_trigger();
+  pdl_wait();
   const float lr = hyper[0], mu = hyper[1], wd = hyper[2], gs = hyper[3];
   float l2 = 0.f;
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -80,6 +82,8 @@ struct PrepEntry {
 __global__ void weight_prep_dgrad_batched_kernel(const __nv_bfloat16* __restrict__ src_base,
                                                  __nv_bfloat16* __restrict__ dst_base,
                                                  const PrepEntry* __restrict__ table, int n_layers) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ __nv_bfloat16 tile[32][33];
   // binary search: last layer whose tile_begin <= blockIdx.x
   int lo = 0, hi = n_layers - 1;
@@ -111,6 +115,8 @@ __global__ void weight_prep_dgrad_batched_kernel(const __nv_bfloat16* __restrict
 // out[n, p*s, q*s, :] = dy[n, p, q, :], zeros elsewhere. 8 channels per thread.
 __global__ void upsample_zero_kernel(const uint4* __restrict__ dy, uint4* __restrict__ out, int N,
                                      int P, int Q, int U, int V, int c8, int stride) {
+  pdl_trigger();
+  pdl_wait();
   const long long total = (long long)N * U * V * c8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -139,6 +145,8 @@ __global__ void f32_to_bf16_kernel(const float4* __restrict__ src, uint2* __rest
 }
 
 __global__ void mul_inplace_kernel(float* __restrict__ a, const float* __restrict__ b, long long n) {
+  pdl_trigger();
+  pdl_wait();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (long long)gridDim.x * blockDim.x)
     a[i] *= b[i];
@@ -161,10 +169,9 @@ extern "C" int drn_sgd_momentum(float* master, float* grad, float* mom, void* sh
                                 void* stream) {
   DRN_REQUIRE(n % 4 == 0, "sgd_momentum: n must be a multiple of 4");
   const long long n4 = n / 4;
-  sgd_momentum_kernel<<<ew_grid(n4, 256), 256, 0, (cudaStream_t)stream>>>(
-      (float4*)master, (float4*)grad, (float4*)mom, (uint2*)shadow_bf16, n4, hyper, l2_sum,
-      zero_grad);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(sgd_momentum_kernel, dim3(ew_grid(n4, 256)), dim3(256), 0, (cudaStream_t)stream,
+                            (float4*)master, (float4*)grad, (float4*)mom, (uint2*)shadow_bf16, n4, hyper, l2_sum,
+      zero_grad));
   return 0;
 }
 
@@ -181,9 +188,8 @@ extern "C" int drn_upsample_zero(const void* dy, void* out, int N, int P, int Q,
                                  int stride, void* stream) {
   DRN_REQUIRE(C % 8 == 0, "upsample_zero: C must be a multiple of 8");
   const long long total = (long long)N * U * V * (C / 8);
-  upsample_zero_kernel<<<ew_grid(total, 256), 256, 0, (cudaStream_t)stream>>>(
-      (const uint4*)dy, (uint4*)out, N, P, Q, U, V, C / 8, stride);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(upsample_zero_kernel, dim3(ew_grid(total, 256)), dim3(256), 0, (cudaStream_t)stream,
+                            (const uint4*)dy, (uint4*)out, N, P, Q, U, V, C / 8, stride));
   return 0;
 }
 
@@ -197,8 +203,8 @@ extern "C" int drn_f32_to_bf16(const float* src, void* dst, long long n, void* s
 
 // a[i] *= b[i]  (used to keep the structurally-zero taps of the space-to-depth stem filter at zero)
 extern "C" int drn_mul_inplace_f32(float* a, const float* b, long long n, void* stream) {
-  mul_inplace_kernel<<<ew_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(a, b, n);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(mul_inplace_kernel, dim3(ew_grid(n, 256)), dim3(256), 0, (cudaStream_t)stream,
+                            a, b, n));
   return 0;
 }
 
@@ -209,8 +215,7 @@ extern "C" int drn_weight_prep_dgrad_batched(const void* w_arena, void* dgrad_ar
                                              int n_layers, int total_tiles, void* stream) {
   static_assert(sizeof(PrepEntry) == 32, "PrepEntry layout is part of the ABI");
   DRN_REQUIRE(n_layers > 0 && total_tiles > 0, "weight_prep_dgrad_batched: empty table");
-  weight_prep_dgrad_batched_kernel<<<total_tiles, dim3(32, 8), 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)w_arena, (__nv_bfloat16*)dgrad_arena, (const PrepEntry*)table, n_layers);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(weight_prep_dgrad_batched_kernel, dim3(total_tiles), dim3(dim3(32, 8)), 0, (cudaStream_t)stream,
+                            (const __nv_bfloat16*)w_arena, (__nv_bfloat16*)dgrad_arena, (const PrepEntry*)table, n_layers));
   return 0;
 }

@@ -35,6 +35,8 @@ __device__ __forceinline__ BF8 pack8(const float (&f)[8]) {
 __global__ void maxpool_fwd_kernel(const BF8* __restrict__ x, BF8* __restrict__ out,
                                    U8x8* __restrict__ argmax, int N, int H, int W, int c8, int P,
                                    int Q, int ksize, int stride, int pad_lo) {
+  pdl_trigger();
+  pdl_wait();
   const long long total = (long long)N * P * Q * c8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -82,6 +84,8 @@ __global__ void maxpool_fwd_kernel(const BF8* __restrict__ x, BF8* __restrict__ 
 __global__ void maxpool3x3s2_fwd_kernel(const BF8* __restrict__ x, BF8* __restrict__ out,
                                         U8x8* __restrict__ argmax, int N, int H, int W, int c8, int P,
                                         int Q, int pad_lo) {
+  pdl_trigger();
+  pdl_wait();
   const long long total = (long long)N * P * Q * c8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -135,6 +139,8 @@ __global__ void maxpool3x3s2_fwd_kernel(const BF8* __restrict__ x, BF8* __restri
 __global__ void maxpool_bwd_kernel(const BF8* __restrict__ dy, const U8x8* __restrict__ argmax,
                                    BF8* __restrict__ dx, int N, int H, int W, int c8, int P, int Q,
                                    int ksize, int stride, int pad_lo) {
+  pdl_trigger();
+  pdl_wait();
   const long long total = (long long)N * H * W * c8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -179,6 +185,8 @@ __global__ void maxpool_bwd_kernel(const BF8* __restrict__ dy, const U8x8* __res
 __global__ void maxpool3x3s2_bwd_kernel(const BF8* __restrict__ dy, const U8x8* __restrict__ argmax,
                                         BF8* __restrict__ dx, int N, int H, int W, int c8, int P,
                                         int Q, int pad_lo, int PI, int QI) {
+  pdl_trigger();
+  pdl_wait();
   const long long total = (long long)N * PI * QI * c8;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
@@ -231,6 +239,8 @@ __global__ void maxpool3x3s2_bwd_kernel(const BF8* __restrict__ dy, const U8x8* 
 __global__ void bnrelu_avgpool_kernel(const BF8* __restrict__ y,
                                       const float2* __restrict__ scale_shift, BF8* __restrict__ out,
                                       int HW, int c8, float inv_hw) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float s_acc[256 * 8];
   const int n = blockIdx.x;
   const int cg = threadIdx.x % c8;
@@ -280,13 +290,13 @@ extern "C" int drn_maxpool_fwd(const void* x, void* out, void* argmax, int N, in
   DRN_REQUIRE(C % 8 == 0, "maxpool: C must be a multiple of 8");
   DRN_REQUIRE(ksize * ksize < 255, "maxpool: window too large");
   const long long total = (long long)N * P * Q * (C / 8);
-  if (ksize == 3 && stride == 2)
-    maxpool3x3s2_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
-        (const BF8*)x, (BF8*)out, (U8x8*)argmax, N, H, W, C / 8, P, Q, pad_lo);
-  else
-    maxpool_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
-        (const BF8*)x, (BF8*)out, (U8x8*)argmax, N, H, W, C / 8, P, Q, ksize, stride, pad_lo);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  if (ksize == 3 && stride == 2) {
+    DRN_CHECK_CUDA(launch_pdl(maxpool3x3s2_fwd_kernel, dim3(grid_for(total)), dim3(256), 0, (cudaStream_t)stream,
+                            (const BF8*)x, (BF8*)out, (U8x8*)argmax, N, H, W, C / 8, P, Q, pad_lo));
+    return 0;
+  }
+  DRN_CHECK_CUDA(launch_pdl(maxpool_fwd_kernel, dim3(grid_for(total)), dim3(256), 0, (cudaStream_t)stream,
+                            (const BF8*)x, (BF8*)out, (U8x8*)argmax, N, H, W, C / 8, P, Q, ksize, stride, pad_lo));
   return 0;
 }
 
@@ -297,15 +307,13 @@ extern "C" int drn_maxpool_bwd(const void* dy, const void* argmax, void* dx, int
   if (ksize == 3 && stride == 2 && pad_lo >= 0 && pad_lo <= 1) {
     const int PI = (H - 1 + pad_lo) / 2 + 1, QI = (W - 1 + pad_lo) / 2 + 1;
     const long long patches = (long long)N * PI * QI * (C / 8);
-    maxpool3x3s2_bwd_kernel<<<grid_for(patches), 256, 0, (cudaStream_t)stream>>>(
-        (const BF8*)dy, (const U8x8*)argmax, (BF8*)dx, N, H, W, C / 8, P, Q, pad_lo, PI, QI);
-    DRN_CHECK_CUDA(cudaGetLastError());
+    DRN_CHECK_CUDA(launch_pdl(maxpool3x3s2_bwd_kernel, dim3(grid_for(patches)), dim3(256), 0, (cudaStream_t)stream,
+                            (const BF8*)dy, (const U8x8*)argmax, (BF8*)dx, N, H, W, C / 8, P, Q, pad_lo, PI, QI));
     return 0;
   }
   const long long total = (long long)N * H * W * (C / 8);
-  maxpool_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
-      (const BF8*)dy, (const U8x8*)argmax, (BF8*)dx, N, H, W, C / 8, P, Q, ksize, stride, pad_lo);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(maxpool_bwd_kernel, dim3(grid_for(total)), dim3(256), 0, (cudaStream_t)stream,
+                            (const BF8*)dy, (const U8x8*)argmax, (BF8*)dx, N, H, W, C / 8, P, Q, ksize, stride, pad_lo));
   return 0;
 }
 
@@ -314,8 +322,7 @@ extern "C" int drn_bnrelu_avgpool(const void* y, const void* scale_shift, void* 
   const int c8 = C / 8;
   DRN_REQUIRE(C % 8 == 0 && c8 <= 256 && (c8 & (c8 - 1)) == 0,
               "bnrelu_avgpool: C=%d must be 8 * a power of two <= 2048", C);
-  bnrelu_avgpool_kernel<<<N, 256, 0, (cudaStream_t)stream>>>(
-      (const BF8*)y, (const float2*)scale_shift, (BF8*)out, HW, c8, 1.f / (float)HW);
-  DRN_CHECK_CUDA(cudaGetLastError());
+  DRN_CHECK_CUDA(launch_pdl(bnrelu_avgpool_kernel, dim3(N), dim3(256), 0, (cudaStream_t)stream,
+                            (const BF8*)y, (const float2*)scale_shift, (BF8*)out, HW, c8, 1.f / (float)HW));
   return 0;
 }
