@@ -359,10 +359,34 @@ __global__ void bn_finalize_apply_kernel(const BF8* __restrict__ y, const float*
                                          BF8* __restrict__ out, long long n_vec, int c8, int relu) {
   pdl_trigger();
   pdl_wait();
-  const long long stride = (long long)gridDim.x * blockDim.x;
+  // The LAST block only publishes the per-channel results (one channel per thread, so the
+  // read-modify-writes of the moving averages are parallel instead of eight dependent round trips
+  // in front of a worker's data loop); all other blocks stream the tensor.
+  if (blockIdx.x == gridDim.x - 1) {
+    for (int c = threadIdx.x; c < c8 * 8; c += blockDim.x) {
+      const float mean = __ldg(stats + c) * inv_count;
+      const float var = fmaxf(fmaf(-mean, mean, __ldg(stats + stats_ld + c) * inv_count), 0.f);
+      const float invstd = rsqrtf(var + eps);
+      const float sc = __ldg(gamma + c) * invstd;
+      scale_shift[c] = make_float2(sc, fmaf(-mean, sc, __ldg(beta + c)));
+      mean_invstd[c] = make_float2(mean, invstd);
+      if (run_mean != nullptr) {
+        run_mean[c] -= (run_mean[c] - mean) * one_minus_decay;
+        run_var[c] -= (run_var[c] - var * unbias) * one_minus_decay;
+      }
+    }
+    return;
+  }
+  const long long stride = (long long)(gridDim.x - 1) * blockDim.x;
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int cg = (int)(i % c8);
-  const bool publish = blockIdx.x == 0 && (int)threadIdx.x < c8;
+  // first pair of data loads before the statistics round trip (see the backward kernel)
+  bool first = i + stride < n_vec;
+  BF8 y0, y1;
+  if (first) {
+    y0 = y[i];
+    y1 = y[i + stride];
+  }
   float2 ss[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
@@ -372,17 +396,13 @@ __global__ void bn_finalize_apply_kernel(const BF8* __restrict__ y, const float*
     const float invstd = rsqrtf(var + eps);
     const float sc = __ldg(gamma + c) * invstd;
     ss[k] = make_float2(sc, fmaf(-mean, sc, __ldg(beta + c)));
-    if (publish) {
-      scale_shift[c] = ss[k];
-      mean_invstd[c] = make_float2(mean, invstd);
-      if (run_mean != nullptr) {
-        run_mean[c] -= (run_mean[c] - mean) * one_minus_decay;
-        run_var[c] -= (run_var[c] - var * unbias) * one_minus_decay;
-      }
-    }
   }
   for (; i + stride < n_vec; i += 2 * stride) {
-    const BF8 y0 = y[i], y1 = y[i + stride];
+    if (!first) {
+      y0 = y[i];
+      y1 = y[i + stride];
+    }
+    first = false;
     float f0[8], f1[8];
     unpack8(y0, f0);
     unpack8(y1, f1);
@@ -442,28 +462,26 @@ __global__ void bn_bwd_finalize_apply_kernel(const BF8* __restrict__ dm, const B
                                              long long n_vec, int c8) {
   pdl_trigger();
   pdl_wait();
-  const long long stride = (long long)gridDim.x * blockDim.x;
+  if (blockIdx.x == gridDim.x - 1) {   // publisher block, see bn_finalize_apply_kernel
+    if (dgamma != nullptr) {
+      for (int c = threadIdx.x; c < c8 * 8; c += blockDim.x) {
+        const float s1 = __ldg(stats + c), s2 = __ldg(stats + stats_ld + c);
+        const float2 mi = __ldg(mean_invstd + c);
+        dgamma[c] += mi.y * (s2 - mi.x * s1);
+        dbeta[c] += s1;
+      }
+    }
+    return;
+  }
+  const long long stride = (long long)(gridDim.x - 1) * blockDim.x;
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int cg = (int)(i % c8);
-  const bool publish = blockIdx.x == 0 && (int)threadIdx.x < c8;
-  float ca[8], cb[8], cc[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const int c = cg * 8 + k;
-    const float s1 = __ldg(stats + c), s2 = __ldg(stats + stats_ld + c);
-    const float2 mi = __ldg(mean_invstd + c);
-    const float dg = mi.y * (s2 - mi.x * s1);
-    if (publish && dgamma != nullptr) {
-      dgamma[c] += dg;
-      dbeta[c] += s1;
-    }
-    ca[k] = __ldg(gamma + c) * mi.y;
-    cb[k] = -ca[k] * mi.y * dg * inv_count;
-    cc[k] = -ca[k] * s1 * inv_count - cb[k] * mi.x;
-  }
+  // the first batch of data loads does not depend on the coefficients: issue it before the
+  // statistics round trip so the two latencies overlap (small tensors are latency-bound)
   const bool has_add = addend != nullptr;
-  for (; i + (U - 1) * stride < n_vec; i += U * stride) {
-    BF8 d[U], t[U], a[U];
+  BF8 d[U], t[U], a[U];
+  bool first = i + (U - 1) * stride < n_vec;
+  if (first) {
 #pragma unroll
     for (int u = 0; u < U; ++u) d[u] = ld_vec<POL>(dm + i + u * stride);
 #pragma unroll
@@ -472,6 +490,30 @@ __global__ void bn_bwd_finalize_apply_kernel(const BF8* __restrict__ dm, const B
 #pragma unroll
       for (int u = 0; u < U; ++u) a[u] = ld_vec<POL>(addend + i + u * stride);
     }
+  }
+  float ca[8], cb[8], cc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cg * 8 + k;
+    const float s1 = __ldg(stats + c), s2 = __ldg(stats + stats_ld + c);
+    const float2 mi = __ldg(mean_invstd + c);
+    const float dg = mi.y * (s2 - mi.x * s1);
+    ca[k] = __ldg(gamma + c) * mi.y;
+    cb[k] = -ca[k] * mi.y * dg * inv_count;
+    cc[k] = -ca[k] * s1 * inv_count - cb[k] * mi.x;
+  }
+  for (; i + (U - 1) * stride < n_vec; i += U * stride) {
+    if (!first) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) d[u] = ld_vec<POL>(dm + i + u * stride);
+#pragma unroll
+      for (int u = 0; u < U; ++u) t[u] = ld_vec<0>(y + i + u * stride);
+      if (has_add) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) a[u] = ld_vec<POL>(addend + i + u * stride);
+      }
+    }
+    first = false;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       float g[8], yy[8];
@@ -625,7 +667,7 @@ extern "C" int drn_bn_finalize_apply(const void* y, const float* stats, int stat
   DRN_REQUIRE(count > 0, "bn_finalize_apply: count must be positive");
   const float unbias = count > 1 ? (float)((double)count / (double)(count - 1)) : 1.f;
   const long long n_vec = count * (C / 8);
-  DRN_CHECK_CUDA(launch_pdl(bn_finalize_apply_kernel, dim3(fused_grid(n_vec)), dim3(kThreads), 0, (cudaStream_t)stream,
+  DRN_CHECK_CUDA(launch_pdl(bn_finalize_apply_kernel, dim3(fused_grid(n_vec) + 1), dim3(kThreads), 0, (cudaStream_t)stream,
                             (const BF8*)y, stats, stats_ld, (float)(1.0 / (double)count), unbias, gamma, beta, run_mean,
       run_var, 1.f - decay, eps, (float2*)scale_shift, (float2*)mean_invstd, (BF8*)out, n_vec, C / 8,
       relu));
@@ -640,7 +682,7 @@ extern "C" int drn_bn_bwd_finalize_apply(const void* dm, const void* y, const fl
   if (int e = check_c(C, "bn_bwd_finalize_apply")) return e;
   const long long n_vec = count * (C / 8);
   static const int variant = getenv("DRN_BN_VARIANT") ? atoi(getenv("DRN_BN_VARIANT")) : 0;
-  const int blocks = fused_grid(n_vec);
+  const int blocks = fused_grid(n_vec) + 1;   // + the publisher block
   auto kern = variant == 1   ? bn_bwd_finalize_apply_kernel<2, 1>
               : variant == 2 ? bn_bwd_finalize_apply_kernel<4, 0>
               : variant == 3 ? bn_bwd_finalize_apply_kernel<4, 1>
