@@ -512,7 +512,10 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   p.pad_h = d.pad_lo;
   p.pad_w = pad_w_lo;
   p.mode = mode;
-  p.n_res = mode == DRN_EPI_PLAIN ? 0 : (env_int("DRN_NRES", 2));
+  // side-input ring: short reductions leave shared memory for a deeper ring (3 chunks of lookahead),
+  // long ones need the pipeline stages more (measured, bench/tune_igemm.py)
+  const int k_iters_total = d.R * d.S * ((d.C + KC - 1) / KC);
+  p.n_res = mode == DRN_EPI_PLAIN ? 0 : env_int("DRN_NRES", k_iters_total <= 2 ? 4 : 2);
   p.n_stages = C_::stages_for(p.n_res);
   if (p.n_stages < 2) return fail("conv_igemm: shared memory plan does not fit (KC=%d BN=%d)", KC, BN);
   const int smem_bytes = C_::smem_for(p.n_res, p.n_stages);
@@ -583,11 +586,19 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
   DRN_REQUIRE(stats == nullptr || stats_ld >= d.K, "conv_igemm: stats_ld < K");
   int bn = force_bn;
   if (bn == 0) {
-    // 256-wide tiles leave room for only two pipeline stages next to the side-input ring: keep
-    // them for shallow reductions, use 128 when the K loop is long
-    const bool deep_k = d.R * d.S * d.C > env_int("DRN_DEEPK", 256);
-    if (d.K % 256 == 0 && !(mode != DRN_EPI_PLAIN && deep_k)) bn = 256;
-    else if (d.K % 128 == 0) bn = 128;
+    // Measured on B200 over every ResNet-50 role (bench/tune_igemm.py): a 256-wide tile costs about
+    // twice a 128-wide one (a little more when a side input is streamed), so it only pays when it
+    // saves a partial round of the persistent grid, or when the reduction is a single k-block and
+    // re-reading the A tile for a second N tile would double the input traffic.
+    const long long m_tiles = (1LL * d.N * d.P * d.Q + 127) / 128;
+    const int k_iters = d.R * d.S * ((d.C + 63) / 64);
+    const int sms = num_sms();
+    if (d.K % 256 == 0) {
+      const long long r128 = (m_tiles * (d.K / 128) + sms - 1) / sms;
+      const long long r256 = (m_tiles * (d.K / 256) + sms - 1) / sms;
+      const double w256 = (mode != DRN_EPI_PLAIN && k_iters < 32) ? 2.2 : 1.9;  // epilogue-heavy when K is short
+      bn = (k_iters == 1 || r256 * w256 < (double)r128) ? 256 : 128;
+    } else if (d.K % 128 == 0) bn = 128;
     else if (d.K % 64 == 0) bn = 64;
     else if (d.K % 32 == 0) bn = 32;
     else bn = 16;
