@@ -52,7 +52,12 @@ struct ConvParams {
   int stats_ld;    // leading dimension of stats rows
   float* stats;    // [2][stats_ld]
   const float2* bn_scale_shift;  // [Cout] (scale, shift) of the BN whose backward mask is applied
+  // PRE variant: the A operand is relu(x * scale + shift) of the RAW tensor x (BatchNorm + ReLU of
+  // the consuming layer applied in shared memory between the TMA load and the MMA)
+  const float2* pre_ss;  // [C] (scale, shift)
+  long long M;           // valid output rows (rows beyond are forced to zero after the transform)
 };
+constexpr int kPreThreads = 128;    // warps 12-15 of the PRE variant
 
 constexpr int kMaxRes = 8;          // side-input ring depth per epilogue group (upper bound)
 constexpr int kSmemBudget = 226 * 1024;
@@ -85,8 +90,8 @@ struct Cfg {
   }
 };
 
-template <int KC, int BN>
-__global__ void __launch_bounds__(kNumThreads, 1)
+template <int KC, int BN, bool PRE = false>
+__global__ void __launch_bounds__(PRE ? kNumThreads + kPreThreads : kNumThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                   const __grid_constant__ CUtensorMap tmapC, const __grid_constant__ CUtensorMap tmapR,
                   const ConvParams p) {
@@ -113,6 +118,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
   auto tempty_bar = [&](int b) { return sBar + 8u * (2 * kMaxStages + 2 + b); };
   auto res_bar = [&](int b) { return sBar + 8u * (2 * kMaxStages + 4 + b); };  // b in [0, 2*kMaxRes)
   const uint32_t sTmemPtr = sBar + 8u * (2 * kMaxStages + 4 + 2 * kMaxRes);
+  auto ready_bar = [&](int s) { return sBar + 8u * (2 * kMaxStages + 4 + 2 * kMaxRes + 1 + s); };  // PRE
   volatile uint32_t* tmem_ptr_gen =
       reinterpret_cast<volatile uint32_t*>(smem_gen + (sTmemPtr - smem_base));
 
@@ -142,6 +148,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
       mbar_init(tempty_bar(b), kEpiThreads * C_::kChunks);  // one arrival per thread per chunk
     }
     for (int b = 0; b < 2 * kMaxRes; ++b) mbar_init(res_bar(b), 1);
+    if (PRE)
+      for (int s = 0; s < kStages; ++s) mbar_init(ready_bar(s), kPreThreads);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -204,7 +212,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int it = 0; it < p.k_iters; ++it) {
-          mbar_wait(full_bar(stage), phase, 0x20 + stage);
+          mbar_wait(PRE ? ready_bar(stage) : full_bar(stage), phase, 0x20 + stage);
           tc_fence_after();
           const uint32_t a_addr = sStages + stage * C_::kStageBytes;
           const uint32_t b_addr = a_addr + C_::kABytes;
@@ -226,7 +234,55 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         if (acc == 0) acc_phase ^= 1;
       }
     }
-  } else if (warp >= 4) {
+  } else if (PRE && warp >= 12) {
+    // ======================= A-operand transform (PRE): BatchNorm + ReLU in shared memory ===========
+    // Thread = (16-byte channel group g of the 128-byte row, 8 rows): a warp touches 4 complete rows
+    // per access (512 contiguous bytes, conflict free).  The 128B swizzle stores logical chunk g of
+    // row r at physical chunk g ^ (r & 7).
+    if constexpr (PRE) {
+      const int tt = threadIdx.x - kNumThreads;
+      const int g = tt & 7;
+      const int r0 = tt >> 3;  // rows r0 + 16 * i
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = t_begin; t < t_end; ++t) {
+        const int n_tile = t / p.m_tiles;
+        const int m_tile = t - n_tile * p.m_tiles;
+        const long long m0 = (long long)m_tile * kBM;
+        for (int it = 0; it < p.k_iters; ++it) {
+          const int cb = it % p.c_blocks;
+          const float4* sp = reinterpret_cast<const float4*>(p.pre_ss + cb * KC + g * 8);
+          float4 q[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) q[k] = __ldg(sp + k);  // (sc0, sh0, sc1, sh1) x 4
+          mbar_wait(full_bar(stage), phase, 0x60 + stage);
+          const uint32_t a_addr = sStages + stage * C_::kStageBytes;
+#pragma unroll
+          for (int i = 0; i < kBM / 16; ++i) {
+            const int row = r0 + 16 * i;
+            const uint32_t addr = a_addr + row * 128 + ((g ^ (row & 7)) << 4);
+            const uint4 v = ld_shared_v4(addr);
+            const uint32_t in[4] = {v.x, v.y, v.z, v.w};
+            uint32_t out[4];
+            const bool live = m0 + row < p.M;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const float a = fmaxf(fmaf(bf16lo(in[k]), q[k].x, q[k].y), 0.f);
+              const float b = fmaxf(fmaf(bf16hi(in[k]), q[k].z, q[k].w), 0.f);
+              out[k] = live ? pack_bf16x2(a, b) : 0u;
+            }
+            st_shared_v4(addr, out[0], out[1], out[2], out[3]);
+          }
+          fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's reads
+          mbar_arrive(ready_bar(stage));
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp >= 4 && warp < 12) {
     // ======================= epilogue: two groups of 4 warps =======================
     // A tile is drained in kChunks column chunks of kCW (<= 32) columns.  With kChunks >= 2 group
     // 0 takes the even chunks of every tile and group 1 the odd ones; with a single chunk per
@@ -541,13 +597,32 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
     tR = tC;
   }
 
+  int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
+  p.pre_ss = reinterpret_cast<const float2*>(current_pre());
+  p.M = M;
+  if (p.pre_ss != nullptr) {
+    if constexpr (KC == 64 && (BN == 64 || BN == 128)) {
+      DRN_REQUIRE(d.R == 1 && d.S == 1 && d.pad_lo == 0 && d.pad_hi == 0 && view == nullptr,
+                  "conv_igemm: the BatchNorm prologue supports 1x1 convolutions only");
+      static bool attr_set_pre = false;
+      if (!attr_set_pre) {
+        DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN, true>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
+        attr_set_pre = true;
+      }
+      DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN, true>, dim3(grid),
+                                     dim3(kNumThreads + kPreThreads), smem_bytes, stream, tA, tB, tC, tR, p));
+      return 0;
+    } else {
+      return fail("conv_igemm: the BatchNorm prologue needs C %% 64 == 0 and an N tile of 64 or 128 (got KC=%d BN=%d)", KC, BN);
+    }
+  }
   static bool attr_set = false;
   if (!attr_set) {
     DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
     attr_set = true;
   }
-  int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
   DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN>, dim3(grid), dim3(kNumThreads), smem_bytes, stream,
                             tA, tB, tC, tR, p));
   return 0;
@@ -598,6 +673,7 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
       const long long r256 = (m_tiles * (d.K / 256) + sms - 1) / sms;
       const double w256 = (mode != DRN_EPI_PLAIN && k_iters < 32) ? 2.2 : 1.9;  // epilogue-heavy when K is short
       bn = (k_iters == 1 || r256 * w256 < (double)r128) ? 256 : 128;
+      if (current_pre() != nullptr) bn = 128;   // the prologue variant exists for N tiles <= 128
     } else if (d.K % 128 == 0) bn = 128;
     else if (d.K % 64 == 0) bn = 64;
     else if (d.K % 32 == 0) bn = 32;
@@ -667,5 +743,23 @@ extern "C" int drn_conv_igemm_view(const drn_conv_desc* desc, const drn_conv_vie
   drn::current_view() = &v;
   const int rc = drn_conv_igemm(desc, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, force_bn, stream);
   drn::current_view() = nullptr;
+  return rc;
+}
+
+// y = conv(relu(x * scale + shift), w): the BatchNorm + ReLU that the reference applies in front of
+// every convolution (batch_norm_relu, resnet_model_official.py:41-50,148-156) is executed on the A tile
+// in shared memory, between the TMA load and the tensor-core read, by four extra warps - the
+// activated tensor is never written to memory.  1x1 convolutions with C % 64 == 0 only.
+extern "C" int drn_conv_igemm_pre(const drn_conv_desc* desc, const void* x, const void* pre_scale_shift,
+                                  const void* w, void* y, const void* side, float* stats, int stats_ld,
+                                  const void* bn_scale_shift, int mode, int force_bn, void* stream) {
+  if (pre_scale_shift == nullptr) return drn::fail("conv_igemm_pre: pre_scale_shift is NULL");
+  if ((reinterpret_cast<uintptr_t>(pre_scale_shift) & 15) != 0)
+    return drn::fail("conv_igemm_pre: pre_scale_shift must be 16-byte aligned");
+  if (force_bn != 0 && force_bn != 64 && force_bn != 128)
+    return drn::fail("conv_igemm_pre: N tile must be 64 or 128");
+  drn::current_pre() = pre_scale_shift;
+  const int rc = drn_conv_igemm(desc, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, force_bn, stream);
+  drn::current_pre() = nullptr;
   return rc;
 }

@@ -29,6 +29,11 @@ const ConvView*& current_view() {
   return v;
 }
 
+const void*& current_pre() {
+  static thread_local const void* v = nullptr;
+  return v;
+}
+
 int pdl_mask() {
   static const int m = []() {
     const char* e = getenv("DRN_PDL");

@@ -80,5 +80,8 @@ struct ConvView {
   int pad_w_lo, pad_w_hi;
 };
 const ConvView*& current_view();
+// Optional BatchNorm+ReLU prologue of the *_pre entry points: float2[C] (scale, shift) applied to the
+// raw input before it is used as an operand (thread-local, set around the ordinary launchers).
+const void*& current_pre();
 
 }  // namespace drn

@@ -69,6 +69,14 @@ int drn_conv_igemm_view(const drn_conv_desc* desc, const drn_conv_view* view, co
                         const void* w, void* y, const void* side, float* stats, int stats_ld,
                         const void* bn_scale_shift, int mode, int force_bn, void* stream);
 
+/* y = conv(relu(x * scale + shift), w): BatchNorm + ReLU of the consuming layer applied to the A tile
+ * in shared memory (four extra warps between the TMA load and the MMA), so the activated tensor is
+ * never materialised.  pre_scale_shift = float2[C], 16-byte aligned.  1x1 convolutions, C % 64 == 0,
+ * N tile 64 or 128. */
+int drn_conv_igemm_pre(const drn_conv_desc* desc, const void* x, const void* pre_scale_shift,
+                       const void* w, void* y, const void* side, float* stats, int stats_ld,
+                       const void* bn_scale_shift, int mode, int force_bn, void* stream);
+
 /* Data gradient (K2) of the convolution described by `desc` (FORWARD geometry):
  *   dx[N,H,W,C] = sum_{k,r,s} dy[N,P,Q,K] (x) w,  given w_dgrad = drn_weight_prep_dgrad(w).
  * Runs the implicit-GEMM kernel above on the equivalent stride-1 problem; for stride > 1 dy is first

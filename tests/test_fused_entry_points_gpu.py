@@ -232,3 +232,36 @@ def test_view_entry_points_equal_the_dense_4x4_convolution():
     assert dw.intact()
     refw = torch.nn.grad.conv2d_weight(xf, (K, 16, 4, 4), dy.float().permute(0, 3, 1, 2)).permute(0, 2, 3, 1)
     assert (dw.t - refw).abs().max() <= 2e-3 * refw.abs().max() + 1e-3
+
+
+@pytest.mark.parametrize("N,H,C,K,st", [(8, 14, 256, 128, 1), (5, 7, 512, 64, 1), (4, 28, 256, 512, 2),
+                                        (3, 56, 64, 256, 1)])
+def test_conv_with_batchnorm_prologue_equals_apply_then_conv(N, H, C, K, st):
+    """drn_conv_igemm_pre (BN+ReLU applied to the A tile in shared memory) against drn_bn_apply
+    followed by the plain convolution: identical bf16 inputs to the tensor core, so the outputs and
+    the fused statistics must agree to rounding of the accumulation order."""
+    from distributed_resnet_tensorflow_b200.ops.conv import ConvGeom
+    nl = _nl()
+    g = ConvGeom.tf_fixed_padding(N, H, H, C, K, 1, st)
+    gen = torch.Generator(device="cuda").manual_seed(6)
+    x = (torch.randn((N, H, H, C), device="cuda", generator=gen) * 1.5).bfloat16()
+    w = (torch.randn((K, 1, 1, C), device="cuda", generator=gen) / C ** 0.5).bfloat16()
+    ss = torch.stack([torch.rand(C, device="cuda", generator=gen) + 0.5,
+                      torch.randn(C, device="cuda", generator=gen) * 0.3], 1).contiguous()
+    a = torch.empty_like(x)
+    nl.call("drn_bn_apply", _p(x), _p(ss), 0, _p(a), N * H * H, C, 1, _st())
+    d = g.desc()
+    want = torch.empty((N, g.P, g.Q, K), dtype=torch.bfloat16, device="cuda")
+    st_want = torch.zeros((2, K), device="cuda")
+    nl.call("drn_conv_igemm", ctypes.byref(d), _p(a), _p(w), _p(want), 0, _p(st_want), K, 0, 0, 0, _st())
+    got = Guarded((N, g.P, g.Q, K), torch.bfloat16)
+    st_got = torch.zeros((2, K), device="cuda")
+    nl.call("drn_conv_igemm_pre", ctypes.byref(d), _p(x), _p(ss), _p(w), _p(got.t), 0, _p(st_got), K, 0, 0, 0, _st())
+    torch.cuda.synchronize()
+    assert got.intact()
+    assert (got.t.float() - want.float()).abs().max() <= 0.01 * want.float().abs().max() + 1e-3
+    assert torch.allclose(st_got, st_want, rtol=2e-3, atol=0.5)
+    # first principles
+    ref = F.conv2d(torch.relu(x.float() * ss[:, 0] + ss[:, 1]).permute(0, 3, 1, 2),
+                   w.float().permute(0, 3, 1, 2), stride=st).permute(0, 2, 3, 1)
+    assert (got.t.float() - ref).abs().max() <= 0.03 * ref.abs().max() + 1e-3
