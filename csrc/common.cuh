@@ -94,6 +94,20 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, uint32_
   }
 }
 
+// The same wait for warps that are NOT on the latency-critical path: sleeping between polls keeps
+// their spin loops from taking issue slots away from the warps that are doing arithmetic on the same
+// scheduler (a spinning try_wait loop issues continuously).
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, uint32_t code,
+                                                uint32_t sleep_ns) {
+  if (mbar_try_wait(bar, parity)) return;
+  uint64_t t0 = globaltimer_ns();
+  uint32_t it = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (sleep_ns) __nanosleep(sleep_ns);
+    if (((++it) & 0xff) == 0 && globaltimer_ns() - t0 > DRN_WATCHDOG_NS) watchdog_fire(code);
+  }
+}
+
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -250,6 +264,13 @@ __device__ __forceinline__ uint32_t swz_off(uint32_t linear_off, uint32_t row_by
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+// max(x, 0) and the conversion of both halves in one instruction (cvt.rn.relu.bf16x2.f32; the first
+// source operand lands in the upper half)
+__device__ __forceinline__ uint32_t pack_relu_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
 }
 __device__ __forceinline__ float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }

@@ -56,6 +56,7 @@ struct ConvParams {
   // the consuming layer applied in shared memory between the TMA load and the MMA)
   const float2* pre_ss;  // [C] (scale, shift)
   long long M;           // valid output rows (rows beyond are forced to zero after the transform)
+  unsigned spin_ns;      // sleep between polls of the non-critical mbarrier waits (0 = spin)
 };
 constexpr int kPreThreads = 128;    // warps 12-15 of the PRE variant
 
@@ -149,7 +150,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     }
     for (int b = 0; b < 2 * kMaxRes; ++b) mbar_init(res_bar(b), 1);
     if (PRE)
-      for (int s = 0; s < kStages; ++s) mbar_init(ready_bar(s), kPreThreads);
+      for (int s = 0; s < kStages; ++s) mbar_init(ready_bar(s), kPreThreads / 32);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -183,7 +184,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           const int cb = it - tap * p.c_blocks;
           const int r = tap / p.S;
           const int s = tap - r * p.S;
-          mbar_wait(empty_bar(stage), phase ^ 1, 0x10 + stage);
+          mbar_wait_sleep(empty_bar(stage), phase ^ 1, 0x10 + stage, p.spin_ns);
           const uint32_t a_dst = sStages + stage * C_::kStageBytes;
           const uint32_t b_dst = a_dst + C_::kABytes;
           mbar_arrive_expect_tx(full_bar(stage), C_::kABytes + C_::kBBytesRaw);
@@ -255,26 +256,34 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           float4 q[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) q[k] = __ldg(sp + k);  // (sc0, sh0, sc1, sh1) x 4
-          mbar_wait(full_bar(stage), phase, 0x60 + stage);
+          mbar_wait_sleep(full_bar(stage), phase, 0x60 + stage, p.spin_ns);
           const uint32_t a_addr = sStages + stage * C_::kStageBytes;
+          // all loads first, then all arithmetic, then all stores: one warp per scheduler has to
+          // find its instruction-level parallelism inside its own stream
+          uint4 v[kBM / 16];
 #pragma unroll
           for (int i = 0; i < kBM / 16; ++i) {
             const int row = r0 + 16 * i;
-            const uint32_t addr = a_addr + row * 128 + ((g ^ (row & 7)) << 4);
-            const uint4 v = ld_shared_v4(addr);
-            const uint32_t in[4] = {v.x, v.y, v.z, v.w};
-            uint32_t out[4];
-            const bool live = m0 + row < p.M;
+            v[i] = ld_shared_v4(a_addr + row * 128 + ((g ^ (row & 7)) << 4));
+          }
+          const bool ragged = m0 + kBM > p.M;   // only the last row tile has rows to blank
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const float a = fmaxf(fmaf(bf16lo(in[k]), q[k].x, q[k].y), 0.f);
-              const float b = fmaxf(fmaf(bf16hi(in[k]), q[k].z, q[k].w), 0.f);
-              out[k] = live ? pack_bf16x2(a, b) : 0u;
-            }
-            st_shared_v4(addr, out[0], out[1], out[2], out[3]);
+          for (int i = 0; i < kBM / 16; ++i) {
+            uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k)   // fp32 fma, then ONE convert-with-ReLU packs both halves
+              w[k] = pack_relu_bf16x2(fmaf(bf16lo(w[k]), q[k].x, q[k].y), fmaf(bf16hi(w[k]), q[k].z, q[k].w));
+            if (ragged && m0 + r0 + 16 * i >= p.M) w[0] = w[1] = w[2] = w[3] = 0u;
+            v[i] = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+#pragma unroll
+          for (int i = 0; i < kBM / 16; ++i) {
+            const int row = r0 + 16 * i;
+            st_shared_v4(a_addr + row * 128 + ((g ^ (row & 7)) << 4), v[i].x, v[i].y, v[i].z, v[i].w);
           }
           fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's reads
-          mbar_arrive(ready_bar(stage));
+          __syncwarp();
+          if (lane == 0) mbar_arrive(ready_bar(stage));   // one arrival per warp
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
@@ -400,7 +409,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
             named_bar_sync(bar_id, kEpiThreads);
           }
         }
-        mbar_wait(tfull_bar(acc), acc_phase, 0x40 + acc);
+        mbar_wait_sleep(tfull_bar(acc), acc_phase, 0x40 + acc, p.spin_ns);
         tc_fence_after();
 
 #pragma unroll
@@ -437,7 +446,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           mbar_arrive(tempty_bar(acc));
 
           if (has_res) {
-            mbar_wait(res_bar(grp * kMaxRes + rb), (mine / n_res) & 1, 0x50 + grp * kMaxRes + rb);
+            mbar_wait_sleep(res_bar(grp * kMaxRes + rb), (mine / n_res) & 1, 0x50 + grp * kMaxRes + rb, p.spin_ns);
             if (p.mode == DRN_EPI_RESADD) {
 #pragma unroll
               for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
@@ -600,6 +609,7 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
   p.pre_ss = reinterpret_cast<const float2*>(current_pre());
   p.M = M;
+  p.spin_ns = (unsigned)env_int("DRN_SPIN_NS", 0);
   if (p.pre_ss != nullptr) {
     if constexpr (KC == 64 && (BN == 64 || BN == 128)) {
       DRN_REQUIRE(d.R == 1 && d.S == 1 && d.pad_lo == 0 && d.pad_hi == 0 && view == nullptr,
