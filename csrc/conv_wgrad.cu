@@ -24,6 +24,7 @@ namespace {
 
 constexpr int kPix = 64;          // pixels (GEMM-K) per pipeline stage
 constexpr int kThreads = 192;     // warp0 TMA, warp1 MMA (+TMEM alloc), warps 2-5 epilogue
+constexpr int kPreThreads = 128;  // PRE variant: warps 6-9 apply BatchNorm+ReLU to the X tiles in smem
 constexpr int kMaxStages = 8;
 
 struct WgradParams {
@@ -38,6 +39,7 @@ struct WgradParams {
   int stride, pad, pad_w;
   int Kout, C;
   float* dw;
+  const float2* pre_ss;  // PRE: (scale, shift) per input channel, X is the RAW tensor
 };
 
 template <int CWA, int CWB>
@@ -64,8 +66,8 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 // (filter tap, input channel) axis - which is exactly the memory order of dW[k][r][s][c] - and a
 // range of output pixels as the reduction.  Every column box of CWB channels is one im2col TMA
 // load (its own tap), so the dY tile is fetched once for up to 16 taps.
-template <int CWA, int CWB>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int CWA, int CWB, bool PRE = false>
+__global__ void __launch_bounds__(PRE ? kThreads + kPreThreads : kThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_constant__ CUtensorMap tmapX,
                   const WgradParams p) {
   using C_ = WCfg<CWA, CWB>;
@@ -79,6 +81,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
   auto empty_bar = [&](int s) { return sBar + 8u * (kMaxStages + s); };
   const uint32_t tfull_bar = sBar + 8u * (2 * kMaxStages);
   const uint32_t sTmemPtr = sBar + 8u * (2 * kMaxStages + 1);
+  auto ready_bar = [&](int s) { return sBar + 8u * (2 * kMaxStages + 2 + s); };  // PRE
   volatile uint32_t* tmem_ptr_gen =
       reinterpret_cast<volatile uint32_t*>(smem_gen + (sTmemPtr - smem_base));
 
@@ -109,6 +112,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
       mbar_init(empty_bar(i), 1);
     }
     mbar_init(tfull_bar, 1);
+    if (PRE)
+      for (int i = 0; i < kStages; ++i) mbar_init(ready_bar(i), kPreThreads / 32);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -170,7 +175,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
         int stage = 0;
         uint32_t phase = 0;
         for (int ch = 0; ch < n_chunks; ++ch) {
-          mbar_wait(full_bar(stage), phase, 0x120 + stage);
+          mbar_wait(PRE ? ready_bar(stage) : full_bar(stage), phase, 0x120 + stage);
           tc_fence_after();
           const uint32_t a_addr = sStages + stage * C_::kStageBytes;
           const uint32_t b_addr = a_addr + C_::kABytes;
@@ -192,7 +197,57 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
         }
         umma_commit(tfull_bar);
       }
-    } else {
+    } else if (PRE && warp >= 6) {
+      // X-tile transform: relu(x * scale + shift) in place, box by box (one box = 64 pixels x 64
+      // channels of ONE filter tap; 128-byte rows, 128B swizzle: logical 16-byte chunk g of row r
+      // sits at physical chunk g ^ (r & 7)).  Out-of-range pixel rows need no masking here: their
+      // dY rows are zero-filled by TMA, so whatever the transform makes of them is multiplied by 0.
+      if constexpr (PRE) {
+        const int tt = threadIdx.x - kThreads;
+        const int g = tt & 7;
+        const int r0 = tt >> 3;  // rows r0 + 16 * j
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int ch = 0; ch < n_chunks; ++ch) {
+          mbar_wait(full_bar(stage), phase, 0x160 + stage);
+          const uint32_t b_addr = sStages + stage * C_::kStageBytes + C_::kABytes;
+          for (int i = 0; i < nboxes; ++i) {
+            const int c0 = (n0 + i * CWB) % p.C;
+            const float4* sp = reinterpret_cast<const float4*>(p.pre_ss + c0 + g * 8);
+            float4 q[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) q[k] = __ldg(sp + k);
+            const uint32_t box = b_addr + i * C_::kBBoxBytes;
+            uint4 v[kPix / 16];
+#pragma unroll
+            for (int j = 0; j < kPix / 16; ++j) {
+              const int row = r0 + 16 * j;
+              v[j] = ld_shared_v4(box + row * 128 + ((g ^ (row & 7)) << 4));
+            }
+#pragma unroll
+            for (int j = 0; j < kPix / 16; ++j) {
+              uint32_t w[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                w[k] = pack_relu_bf16x2(fmaf(bf16lo(w[k]), q[k].x, q[k].y), fmaf(bf16hi(w[k]), q[k].z, q[k].w));
+              v[j] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+#pragma unroll
+            for (int j = 0; j < kPix / 16; ++j) {
+              const int row = r0 + 16 * j;
+              st_shared_v4(box + row * 128 + ((g ^ (row & 7)) << 4), v[j].x, v[j].y, v[j].z, v[j].w);
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(ready_bar(stage));
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    } else if (warp < 6) {
       // epilogue: warps 2..5 -> TMEM lane quadrants 2,3,0,1
       const int quad = warp & 3;
       const int row = quad * 32 + lane;
@@ -272,6 +327,7 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
   p.Kout = d.K;
   p.C = d.C;
   p.dw = dw;
+  p.pre_ss = reinterpret_cast<const float2*>(current_pre());
 
   CUtensorMap tDY, tX;
   if (int e = tmap_tiled_2d(&tDY, dy, 2, (uint64_t)M, d.K, d.K, kPix, CWA, C_::kRBA)) return e;
@@ -287,6 +343,21 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
     attr_set = true;
   }
   const int grid = units * splits;
+  if (p.pre_ss != nullptr) {
+    if constexpr (CWB == 64) {
+      static bool attr_set_pre = false;
+      if (!attr_set_pre) {
+        DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<CWA, CWB, true>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, C_::kSmemBytes));
+        attr_set_pre = true;
+      }
+      DRN_CHECK_CUDA(launch_pdl_conv(conv_wgrad_kernel<CWA, CWB, true>, dim3(grid), dim3(kThreads + kPreThreads),
+                                     C_::kSmemBytes, stream, tDY, tX, p));
+      return 0;
+    } else {
+      return fail("conv_wgrad: the BatchNorm prologue needs C %% 64 == 0");
+    }
+  }
   DRN_CHECK_CUDA(launch_pdl_conv(conv_wgrad_kernel<CWA, CWB>, dim3(grid), dim3(kThreads), C_::kSmemBytes, stream,
                             tDY, tX, p));
   return 0;
@@ -323,5 +394,18 @@ extern "C" int drn_conv_wgrad_view(const drn_conv_desc* desc, const drn_conv_vie
   drn::current_view() = &v;
   const int rc = drn_conv_wgrad(desc, x, dy, dw, split_k, stream);
   drn::current_view() = nullptr;
+  return rc;
+}
+
+// dw += dY (x) relu(x * scale + shift): filter gradient of a convolution whose input is the
+// BatchNorm+ReLU of the RAW tensor x - the activation is rebuilt in shared memory (see
+// drn_conv_igemm_pre), so the forward pass never has to store it.  C % 64 == 0.
+extern "C" int drn_conv_wgrad_pre(const drn_conv_desc* desc, const void* x, const void* pre_scale_shift,
+                                  const void* dy, float* dw, int split_k, void* stream) {
+  if (pre_scale_shift == nullptr || (reinterpret_cast<uintptr_t>(pre_scale_shift) & 15) != 0)
+    return drn::fail("conv_wgrad_pre: pre_scale_shift must be a 16-byte aligned float2[C]");
+  drn::current_pre() = pre_scale_shift;
+  const int rc = drn_conv_wgrad(desc, x, dy, dw, split_k, stream);
+  drn::current_pre() = nullptr;
   return rc;
 }

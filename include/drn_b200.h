@@ -107,6 +107,11 @@ int drn_conv_wgrad(const drn_conv_desc* desc, const void* x, const void* dy, flo
                    int split_k, void* stream);
 
 
+/* dw += dy (x) relu(x * scale + shift): the activation is rebuilt from the RAW tensor in shared memory
+ * (counterpart of drn_conv_igemm_pre).  C % 64 == 0; pre_scale_shift = float2[C], 16-byte aligned. */
+int drn_conv_wgrad_pre(const drn_conv_desc* desc, const void* x, const void* pre_scale_shift,
+                       const void* dy, float* dw, int split_k, void* stream);
+
 int drn_conv_wgrad_view(const drn_conv_desc* desc, const drn_conv_view* view, const void* x,
                         const void* dy, float* dw, int split_k, void* stream);
 

@@ -265,3 +265,27 @@ def test_conv_with_batchnorm_prologue_equals_apply_then_conv(N, H, C, K, st):
     ref = F.conv2d(torch.relu(x.float() * ss[:, 0] + ss[:, 1]).permute(0, 3, 1, 2),
                    w.float().permute(0, 3, 1, 2), stride=st).permute(0, 2, 3, 1)
     assert (got.t.float() - ref).abs().max() <= 0.03 * ref.abs().max() + 1e-3
+
+
+@pytest.mark.parametrize("N,H,C,K,st", [(8, 14, 256, 128, 1), (5, 7, 512, 64, 1), (4, 28, 256, 512, 2),
+                                        (3, 56, 64, 256, 1)])
+def test_wgrad_with_batchnorm_prologue_equals_apply_then_wgrad(N, H, C, K, st):
+    from distributed_resnet_tensorflow_b200.ops.conv import ConvGeom
+    nl = _nl()
+    g = ConvGeom.tf_fixed_padding(N, H, H, C, K, 1, st)
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    x = (torch.randn((N, H, H, C), device="cuda", generator=gen) * 1.5).bfloat16()
+    dy = torch.randn((N, g.P, g.Q, K), device="cuda", generator=gen).bfloat16()
+    ss = torch.stack([torch.rand(C, device="cuda", generator=gen) + 0.5,
+                      torch.randn(C, device="cuda", generator=gen) * 0.3], 1).contiguous()
+    a = torch.empty_like(x)
+    nl.call("drn_bn_apply", _p(x), _p(ss), 0, _p(a), N * H * H, C, 1, _st())
+    d = g.desc()
+    want = torch.zeros((K, 1, 1, C), device="cuda")
+    nl.call("drn_conv_wgrad", ctypes.byref(d), _p(a), _p(dy), _p(want), 0, _st())
+    got = Guarded((K, 1, 1, C), torch.float32)
+    got.t.zero_()
+    nl.call("drn_conv_wgrad_pre", ctypes.byref(d), _p(x), _p(ss), _p(dy), _p(got.t), 0, _st())
+    torch.cuda.synchronize()
+    assert got.intact()
+    assert (got.t - want).abs().max() <= 1e-3 * want.abs().max() + 1e-3
