@@ -35,6 +35,21 @@ from .spec import BlockSpec, BNSpec, ConvSpec, NetSpec
 BN_DECAY = 0.997
 # filter gradients on a second stream (DRN_WGRAD_STREAM=0 keeps everything on one stream)
 WGRAD_SIDE_STREAM = os.environ.get("DRN_WGRAD_STREAM", "1") != "0"
+# first BatchNorm+ReLU of a bottleneck block applied inside its consumers (drn_conv_igemm_pre /
+# drn_conv_wgrad_pre) instead of being written to memory; DRN_FUSE_BN0=0 restores the separate pass
+FUSE_BN0 = os.environ.get("DRN_FUSE_BN0", "1") != "0"
+
+
+def _fuse_bn0(blk: BlockSpec) -> bool:
+    """Where the prologue variant is a measured win (bench/prof_pre.py and bench.py A/B on one B200):
+    1x1 first convolution over 256 or 512 input channels (at 1024 the A tile is re-transformed once
+    per 128-column N tile and the gain vanishes); with a projection shortcut only at 256 channels."""
+    c0 = blk.convs[0]
+    if not FUSE_BN0 or c0.ksize != 1 or c0.stride != 1 or len(blk.convs) != 3:
+        return False
+    if blk.cin not in (256, 512, 1024) or blk.cin > int(os.environ.get("DRN_FUSE_BN0_MAXC", "512")):
+        return False
+    return blk.proj is None or blk.cin == 256
 BN_EPS = 1e-5
 VGG_MEANS = (123.68 / 255.0, 116.78 / 255.0, 103.94 / 255.0)  # vgg_preprocessing.py:37-39 (in [0,1] units)
 
@@ -342,8 +357,9 @@ class NativeResNet:
         B = self.B
         d = {"spec": blk}
         d["bn0"] = _BN(blk.bns[0], self)
-        d["a0"] = self._act(B, blk.hin, blk.hin, blk.cin)
-        sizes = [d["a0"].numel()]
+        d["fuse"] = _fuse_bn0(blk)
+        d["a0"] = None if d["fuse"] else self._act(B, blk.hin, blk.hin, blk.cin)
+        sizes = [B * blk.hin * blk.hin * blk.cin]
         if blk.proj is not None:
             d["proj"] = _Conv(blk.proj, self, self._geom(blk.proj), need_dgrad=True)
             pg = d["proj"].g
@@ -451,7 +467,12 @@ class NativeResNet:
         _nl.call("drn_weight_prep_dgrad_batched", _p(self.shadow), _p(self._wd_arena), _p(self._prep_table),
                  self._prep_layers, self._prep_tiles, self._st() if stream_handle is None else stream_handle)
 
-    def _conv(self, desc, x, w, y, side=None, stats=None, ss=None, mode=EPI_PLAIN):
+    def _conv(self, desc, x, w, y, side=None, stats=None, ss=None, mode=EPI_PLAIN, pre=None):
+        """``pre``: (scale, shift) table of a BatchNorm+ReLU to apply to ``x`` on the fly."""
+        if pre is not None:
+            _nl.call("drn_conv_igemm_pre", ctypes.byref(desc), _p(x), _p(pre), _p(w), _p(y), _p(side), _p(stats),
+                     stats.stride(0) if stats is not None else 0, _p(ss), mode, 0, self._st())
+            return
         _nl.call("drn_conv_igemm", ctypes.byref(desc), _p(x), _p(w), _p(y), _p(side), _p(stats),
                  stats.stride(0) if stats is not None else 0, _p(ss), mode, 0, self._st())
 
@@ -493,7 +514,11 @@ class NativeResNet:
             torch.cuda.current_stream().wait_event(self._wg_last)
             self._wg_last = None
 
-    def _wgrad(self, conv: _Conv, x, dy, dy_idx: Optional[int] = None):
+    def _wgrad(self, conv: _Conv, x, dy, dy_idx: Optional[int] = None, pre=None):
+        if pre is not None:
+            self._on_wgrad_stream(lambda st: _nl.call("drn_conv_wgrad_pre", ctypes.byref(conv.desc), _p(x), _p(pre),
+                                                      _p(dy), _p(conv.dw), 0, st), dy_idx)
+            return
         self._on_wgrad_stream(lambda st: _nl.call("drn_conv_wgrad", ctypes.byref(conv.desc), _p(x), _p(dy),
                                                   _p(conv.dw), 0, st), dy_idx)
 
@@ -567,13 +592,19 @@ class NativeResNet:
     def _block_fwd(self, b: dict, x, next_bn: _BN, training: bool):
         bn0 = b["bn0"]
         b["x"] = x
-        self._bn_fwd(bn0, x, b["a0"], training)
+        if b["fuse"]:
+            # only the per-channel scale/shift (and the moving averages) are computed here; the
+            # consumers of relu(bn0(x)) apply it to their tiles of the raw x in shared memory
+            self._bn_finalize(bn0, x.numel() // bn0.C, training)
+            h, pre = x, bn0.ss
+        else:
+            self._bn_fwd(bn0, x, b["a0"], training)
+            h, pre = b["a0"], None
         shortcut = x
         if "proj" in b:
             pj = b["proj"]
-            self._conv(pj.desc, b["a0"], pj.w, b["shortcut"])
+            self._conv(pj.desc, h, pj.w, b["shortcut"], pre=pre)
             shortcut = b["shortcut"]
-        h = b["a0"]
         convs = b["convs"]
         for i, c in enumerate(convs):
             last = i + 1 == len(convs)
@@ -583,7 +614,7 @@ class NativeResNet:
                            stats=next_bn.fstats if training else None)
             else:
                 bn = b["bns"][i]
-                self._conv(c.desc, h, c.w, y, stats=bn.fstats if training else None)
+                self._conv(c.desc, h, c.w, y, stats=bn.fstats if training else None, pre=pre if i == 0 else None)
                 self._bn_fwd(bn, y, b["acts"][i], training)
                 h = b["acts"][i]
         return b["ys"][-1]
@@ -721,11 +752,14 @@ class NativeResNet:
             self._put(dm_i)
             dy_i, dy = n_i, ndy
         c0 = convs[0]
-        self._wgrad(c0, a0, dy, dy_i)
+        pre0 = bn0.ss if b["fuse"] else None
+        if b["fuse"]:
+            a0 = x          # the filter gradients rebuild relu(bn0(x)) from the raw tensor
+        self._wgrad(c0, a0, dy, dy_i, pre=pre0)
         Bn, H, W, C = x.shape
         if "proj" in b:
             pj = b["proj"]
-            self._wgrad(pj, a0, g, g_i)
+            self._wgrad(pj, a0, g, g_i, pre=pre0)
             da_i, da = self._get(x)
             self._dgrad(c0, dy, da)
             if dy_i != g_i:
