@@ -206,7 +206,15 @@ __global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8*
   for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
   for (long long m = (long long)blockIdx.x * lanes + pl; m < M; m += (long long)gridDim.x * lanes) {
     float g[8], yy[8];
-    if (da != nullptr) {
+    if (addend_kind == 4) {  // da = four parity-phase tensors [4][N][H/2][W/2][C] of a strided dgrad
+      const int w = (int)(m % W);
+      const long long t = m / W;
+      const int h = (int)(t % H);
+      const long long n = t / H;
+      const int Hh = H >> 1, Wh = W >> 1;
+      const long long ph = (long long)((h & 1) * 2 + (w & 1)) * (M >> 2);
+      unpack8(da[(ph + (n * Hh + (h >> 1)) * Wh + (w >> 1)) * c8 + cg], g);
+    } else if (da != nullptr) {
       unpack8(da[m * c8 + cg], g);
     } else {
 #pragma unroll
@@ -625,8 +633,10 @@ extern "C" int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int ad
                                       const void* y, const void* scale_shift, void* dm, float* stats,
                                       int stats_ld, int C, void* stream) {
   if (int e = check_c(C, "bn_bwd_mask_reduce")) return e;
-  DRN_REQUIRE(addend_kind >= 0 && addend_kind <= 3, "bn_bwd_mask_reduce: bad addend_kind");
-  DRN_REQUIRE(addend_kind == 0 || addend != nullptr, "bn_bwd_mask_reduce: addend missing");
+  DRN_REQUIRE(addend_kind >= 0 && addend_kind <= 4, "bn_bwd_mask_reduce: bad addend_kind");
+  DRN_REQUIRE(addend_kind == 0 || addend_kind == 4 || addend != nullptr, "bn_bwd_mask_reduce: addend missing");
+  DRN_REQUIRE(addend_kind != 4 || (da != nullptr && H % 2 == 0 && W % 2 == 0),
+              "bn_bwd_mask_reduce: phase-compact gradients need even H and W");
   DRN_REQUIRE(da != nullptr || addend_kind != 0, "bn_bwd_mask_reduce: no gradient given");
   const long long M = (long long)N * H * W;
   const int lanes = kThreads / (C / 8);

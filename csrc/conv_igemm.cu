@@ -773,3 +773,37 @@ extern "C" int drn_conv_igemm_pre(const drn_conv_desc* desc, const void* x, cons
   drn::current_pre() = nullptr;
   return rc;
 }
+
+// Data gradient of a 3x3 / stride-2 / pad-(1,1) convolution WITHOUT zero insertion: the four parity
+// phases of dx are four small stride-1 convolutions over dy ((1+a) x (1+b) taps, banks from
+// drn_weight_prep_dgrad_s2), 9 tap-GEMMs over P*Q pixels in total instead of 9 over H*W.
+//   out = [4][N][H/2][W/2][C] bf16, phase (a,b) at index a*2+b holds dx[:, a::2, b::2, :].
+// drn_bn_bwd_mask_reduce(addend_kind = 4) interleaves the phases while applying the BN/ReLU mask.
+extern "C" int drn_conv_dgrad_s2(const drn_conv_desc* desc, const void* dy, const void* banks, void* out,
+                                 void* stream) {
+  using namespace drn;
+  const drn_conv_desc& d = *desc;
+  DRN_REQUIRE(d.R == 3 && d.S == 3 && d.stride == 2 && d.pad_lo == 1 && d.pad_hi == 1 && d.H % 2 == 0 &&
+                  d.W % 2 == 0 && d.P == d.H / 2 && d.Q == d.W / 2,
+              "conv_dgrad_s2: needs a 3x3 / stride 2 / pad (1,1) convolution over even H and W");
+  const long long phase_elems = 1LL * d.N * d.P * d.Q * d.C;
+  long long bank_off = 0;
+  for (int a = 0; a < 2; ++a) {
+    for (int b = 0; b < 2; ++b) {
+      drn_conv_desc g;
+      g.N = d.N; g.H = d.P; g.W = d.Q; g.C = d.K; g.K = d.C;
+      g.R = 1 + a; g.S = 1 + b; g.stride = 1;
+      g.pad_lo = 0; g.pad_hi = a;           // rows: dy row i (+ row i+1 for odd output rows)
+      g.P = d.P; g.Q = d.Q;
+      drn_conv_view v;
+      v.stride_w = d.K; v.stride_h = 1LL * d.Q * d.K; v.stride_n = 1LL * d.P * d.Q * d.K;
+      v.pad_w_lo = 0; v.pad_w_hi = b;
+      const char* bank = static_cast<const char*>(banks) + 2 * bank_off;
+      char* dst = static_cast<char*>(out) + 2 * phase_elems * (a * 2 + b);
+      if (int e = drn_conv_igemm_view(&g, &v, dy, bank, dst, nullptr, nullptr, 0, nullptr, DRN_EPI_PLAIN, 0, stream))
+        return e;
+      bank_off += 1LL * (1 + a) * (1 + b) * d.K * d.C;
+    }
+  }
+  return 0;
+}

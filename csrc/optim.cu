@@ -158,6 +158,45 @@ int ew_grid(long long n, int threads) {
   return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
 }
 
+
+// Filter banks of the four parity phases of a 3x3 / stride-2 / pad-1 data gradient.
+// dx[2i+a][2j+b] only receives the filter rows r with (a + 1 - r) even: a = 0 -> {r = 1};
+// a = 1 -> {r = 2 (dy row i), r = 0 (dy row i + 1)}, likewise for columns.  Bank (a,b) is the filter
+// of a stride-1 convolution over dy with (1+a) x (1+b) taps, stored [C][1+a][1+b][K]:
+//   bank[c][tr][ts][k] = w[k][rmap(a,tr)][rmap(b,ts)][c],  rmap(0,0) = 1, rmap(1,0) = 2, rmap(1,1) = 0.
+__global__ void weight_prep_dgrad_s2_kernel(const __nv_bfloat16* __restrict__ w,
+                                            __nv_bfloat16* __restrict__ banks, int K, int C) {
+  pdl_trigger();
+  pdl_wait();
+  const long long total = 9LL * K * C;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    // decode the destination: phase banks are laid out back to back with 1, 2, 2, 4 taps
+    const long long ck = (long long)C * K;
+    long long rem = idx;
+    int phase = 0, taps = 1;
+    const int ntaps[4] = {1, 2, 2, 4};
+#pragma unroll
+    for (int ph = 0; ph < 4; ++ph) {
+      if (rem >= 0 && rem < ntaps[ph] * ck) {
+        phase = ph;
+        taps = ntaps[ph];
+        break;
+      }
+      rem -= ntaps[ph] * ck;
+    }
+    const int a = phase >> 1, b = phase & 1;
+    const int k = (int)(rem % K);
+    long long t = rem / K;
+    const int tap = (int)(t % taps);
+    const int c = (int)(t / taps);
+    const int tr = tap / (1 + b), ts = tap % (1 + b);
+    const int r = a == 0 ? 1 : (tr == 0 ? 2 : 0);
+    const int s_ = b == 0 ? 1 : (ts == 0 ? 2 : 0);
+    banks[idx] = w[((long long)k * 9 + r * 3 + s_) * C + c];
+  }
+}
+
 }  // namespace
 }  // namespace drn
 
@@ -217,5 +256,13 @@ extern "C" int drn_weight_prep_dgrad_batched(const void* w_arena, void* dgrad_ar
   DRN_REQUIRE(n_layers > 0 && total_tiles > 0, "weight_prep_dgrad_batched: empty table");
   DRN_CHECK_CUDA(launch_pdl(weight_prep_dgrad_batched_kernel, dim3(total_tiles), dim3(dim3(32, 8)), 0, (cudaStream_t)stream,
                             (const __nv_bfloat16*)w_arena, (__nv_bfloat16*)dgrad_arena, (const PrepEntry*)table, n_layers));
+  return 0;
+}
+
+// Four phase banks (9*K*C elements, phases (0,0) (0,1) (1,0) (1,1) back to back) for drn_conv_dgrad_s2.
+extern "C" int drn_weight_prep_dgrad_s2(const void* w_krsc, void* banks, int K, int C, void* stream) {
+  const long long total = 9LL * K * C;
+  DRN_CHECK_CUDA(launch_pdl(weight_prep_dgrad_s2_kernel, dim3(ew_grid(total, 256)), dim3(256), 0,
+                            (cudaStream_t)stream, (const __nv_bfloat16*)w_krsc, (__nv_bfloat16*)banks, K, C));
   return 0;
 }

@@ -87,6 +87,15 @@ int drn_conv_dgrad(const drn_conv_desc* desc, const void* dy, const void* w_dgra
                    const void* side, float* stats, int stats_ld, const void* bn_scale_shift, int mode,
                    void* scratch, long long scratch_bytes, void* stream);
 
+/* Data gradient of a 3x3 / stride-2 / pad-(1,1) convolution as four parity-phase stride-1
+ * convolutions over dy (no zero insertion: a quarter of the tensor-core work of drn_conv_dgrad).
+ * banks = drn_weight_prep_dgrad_s2(w) (9*K*C bf16); out = [4][N][H/2][W/2][C] bf16 with phase
+ * (a,b) at index a*2+b holding dx[:, a::2, b::2, :]; drn_bn_bwd_mask_reduce(addend_kind = 4) or any
+ * other consumer interleaves them. */
+int drn_weight_prep_dgrad_s2(const void* w_krsc, void* banks, int K, int C, void* stream);
+int drn_conv_dgrad_s2(const drn_conv_desc* desc, const void* dy, const void* banks, void* out,
+                      void* stream);
+
 /* Same operation as drn_conv_dgrad for callers that cannot allocate device memory when they call -
  * e.g. a process that gave the whole GPU to its own memory pool, or a latency-critical loop where
  * cudaMalloc/cudaFree (which synchronise the device) are off limits.  The zero-insertion scratch
@@ -142,7 +151,9 @@ int drn_bn_bwd_finalize_apply(const void* dm, const void* y, const float* stats,
 int drn_bn_stats(const void* y, float* stats, int stats_ld, long long M, int C, void* stream);
 /* dm = (da [+ addend]) * [y*scale+shift > 0]; stats += (sum dm, sum dm*y).
  * addend_kind: 0 none, 1 same shape, 2 compact stride-2 tensor [N,Ha,Wa,C] added at even pixels,
- * 3 per-image vector [N][C] times bcast_scale (average-pool gradient; da may then be NULL). */
+ * 3 per-image vector [N][C] times bcast_scale (average-pool gradient; da may then be NULL),
+ * 4 no addend, but da is the output of drn_conv_dgrad_s2: four parity-phase tensors
+ *   [4][N][H/2][W/2][C], phase = (h & 1) * 2 + (w & 1). */
 int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int addend_kind, int N, int H, int W,
                            int Ha, int Wa, float bcast_scale, const void* y, const void* scale_shift,
                            void* dm, float* stats, int stats_ld, int C, void* stream);

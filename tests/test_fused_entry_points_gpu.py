@@ -289,3 +289,44 @@ def test_wgrad_with_batchnorm_prologue_equals_apply_then_wgrad(N, H, C, K, st):
     torch.cuda.synchronize()
     assert got.intact()
     assert (got.t - want).abs().max() <= 1e-3 * want.abs().max() + 1e-3
+
+
+@pytest.mark.parametrize("N,H,C,K", [(4, 16, 64, 128), (2, 28, 128, 128), (3, 14, 256, 64)])
+def test_stride2_dgrad_by_parity_phases(N, H, C, K):
+    """drn_conv_dgrad_s2 (four stride-1 phase convolutions over dy) + the interleaving mask/reduce
+    kernel against torch's conv2d_input of the 3x3/stride-2 convolution."""
+    from distributed_resnet_tensorflow_b200.ops.conv import ConvGeom
+    nl = _nl()
+    g = ConvGeom.tf_fixed_padding(N, H, H, C, K, 3, 2)
+    assert (g.pad_lo, g.pad_hi, g.P) == (1, 1, H // 2)
+    gen = torch.Generator(device="cuda").manual_seed(8)
+    w = (torch.randn((K, 3, 3, C), device="cuda", generator=gen) / (9 * C) ** 0.5).bfloat16()
+    dy = torch.randn((N, g.P, g.Q, K), device="cuda", generator=gen).bfloat16()
+    banks = Guarded((9 * K * C,), torch.bfloat16)
+    nl.call("drn_weight_prep_dgrad_s2", _p(w), _p(banks.t), K, C, _st())
+    phases = Guarded((4, N, H // 2, H // 2, C), torch.bfloat16)
+    d = g.desc()
+    nl.call("drn_conv_dgrad_s2", ctypes.byref(d), _p(dy), _p(banks.t), _p(phases.t), _st())
+    torch.cuda.synchronize()
+    assert banks.intact() and phases.intact()
+    ref = torch.nn.grad.conv2d_input((N, C, H + 2, H + 2), w.float().permute(0, 3, 1, 2),
+                                     dy.float().permute(0, 3, 1, 2), stride=2)
+    ref = ref[:, :, 1:1 + H, 1:1 + H].permute(0, 2, 3, 1)
+    got = torch.empty((N, H, H, C), device="cuda")
+    for a in range(2):
+        for b in range(2):
+            got[:, a::2, b::2, :] = phases.t[a * 2 + b].float()
+    assert (got - ref).abs().max() <= 0.02 * ref.abs().max() + 1e-3
+    # interleave + mask + reductions in one pass
+    y = torch.randn((N, H, H, C), device="cuda", generator=gen).bfloat16()
+    ss = torch.stack([torch.ones(C, device="cuda"), torch.zeros(C, device="cuda")], 1).contiguous()
+    dm = Guarded((N, H, H, C), torch.bfloat16)
+    stats = torch.zeros((2, C), device="cuda")
+    nl.call("drn_bn_bwd_mask_reduce", _p(phases.t), 0, 4, N, H, H, 0, 0, 0.0, _p(y), _p(ss), _p(dm.t), _p(stats),
+            C, C, _st())
+    torch.cuda.synchronize()
+    assert dm.intact()
+    want = got.bfloat16().float() * (y.float() > 0)
+    assert (dm.t.float() - want).abs().max() <= 1e-2 * want.abs().max() + 1e-3
+    assert torch.allclose(stats[0], dm.t.float().reshape(-1, C).sum(0), rtol=1e-3, atol=0.05)
+    assert torch.allclose(stats[1], (dm.t.float() * y.float()).reshape(-1, C).sum(0), rtol=1e-3, atol=0.05)
