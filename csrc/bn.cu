@@ -186,8 +186,9 @@ __global__ void bn_stats_kernel(const BF8* __restrict__ y, float* __restrict__ s
 // addend may be a stride-2 "compact" tensor [N, H/2.., W/2.., C] that is added at even pixels
 // (the gradient of a 1x1/stride-2 projection shortcut), or a per-image vector [N][C] scaled by
 // `bcast_scale` (the gradient of the global average pool).
+template <int KIND>
 __global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8* __restrict__ addend,
-                                          int addend_kind, int H, int W, int Ha, int Wa,
+                                          int H, int W, int Ha, int Wa,
                                           float bcast_scale, const BF8* __restrict__ y,
                                           const float2* __restrict__ scale_shift,
                                           BF8* __restrict__ dm, float* __restrict__ stats,
@@ -204,50 +205,62 @@ __global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8*
   float s1[8], s2[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
-  for (long long m = (long long)blockIdx.x * lanes + pl; m < M; m += (long long)gridDim.x * lanes) {
-    float g[8], yy[8];
-    if (addend_kind == 4) {  // da = four parity-phase tensors [4][N][H/2][W/2][C] of a strided dgrad
-      const int w = (int)(m % W);
-      const long long t = m / W;
-      const int h = (int)(t % H);
-      const long long n = t / H;
-      const int Hh = H >> 1, Wh = W >> 1;
+
+  // raw loads of one pixel's 8 channels: gradient, optional addend, pre-activation
+  struct Px {
+    BF8 g, a, y;
+    bool has_g, has_a;
+  };
+  auto fetch = [&](long long m) {
+    Px p;
+    p.has_g = true;
+    p.has_a = false;
+    if (KIND == 4) {  // da = four parity-phase tensors [4][N][H/2][W/2][C] of a strided dgrad
+      // 32-bit index arithmetic (the launcher checks M < 2^31): 64-bit div/mod would cost more
+      // instructions than the rest of the pixel
+      const unsigned mi = (unsigned)m, w = mi % (unsigned)W, t = mi / (unsigned)W;
+      const unsigned h = t % (unsigned)H, n = t / (unsigned)H;
       const long long ph = (long long)((h & 1) * 2 + (w & 1)) * (M >> 2);
-      unpack8(da[(ph + (n * Hh + (h >> 1)) * Wh + (w >> 1)) * c8 + cg], g);
+      p.g = da[(ph + ((long long)n * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * c8 + cg];
     } else if (da != nullptr) {
-      unpack8(da[m * c8 + cg], g);
+      p.g = da[m * c8 + cg];
+    } else {
+      p.has_g = false;
+    }
+    p.y = y[m * c8 + cg];
+    if (KIND == 1) {
+      p.a = addend[m * c8 + cg];
+      p.has_a = true;
+    } else if (KIND == 2) {  // compact stride-2 tensor added at even pixels
+      const unsigned mi = (unsigned)m, w = mi % (unsigned)W, t = mi / (unsigned)W;
+      const unsigned h = t % (unsigned)H, n = t / (unsigned)H;
+      if (((h | w) & 1) == 0 && (int)(h >> 1) < Ha && (int)(w >> 1) < Wa) {
+        p.a = addend[(((long long)n * Ha + (h >> 1)) * Wa + (w >> 1)) * c8 + cg];
+        p.has_a = true;
+      }
+    } else if (KIND == 3) {  // per-image vector
+      p.a = addend[(long long)((unsigned)m / (unsigned)(H * W)) * c8 + cg];
+      p.has_a = true;
+    }
+    return p;
+  };
+  auto finish = [&](long long m, const Px& p) {
+    float g[8], yy[8];
+    if (p.has_g) {
+      unpack8(p.g, g);
     } else {
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] = 0.f;
     }
-    unpack8(y[m * c8 + cg], yy);
-    if (addend_kind == 1) {  // same shape
+    unpack8(p.y, yy);
+    if (p.has_a) {
       float a[8];
-      unpack8(addend[m * c8 + cg], a);
+      unpack8(p.a, a);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] += a[k];
-    } else if (addend_kind == 2) {  // compact stride-2 tensor
-      const int w = (int)(m % W);
-      const long long t = m / W;
-      const int h = (int)(t % H);
-      const long long n = t / H;
-      if (((h | w) & 1) == 0 && (h >> 1) < Ha && (w >> 1) < Wa) {
-        float a[8];
-        unpack8(addend[((n * Ha + (h >> 1)) * Wa + (w >> 1)) * c8 + cg], a);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) g[k] += a[k];
-      }
-    } else if (addend_kind == 3) {  // per-image broadcast
-      const long long n = m / ((long long)H * W);
-      float a[8];
-      unpack8(addend[n * c8 + cg], a);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] = fmaf(a[k], bcast_scale, g[k]);
+      for (int k = 0; k < 8; ++k) g[k] = KIND == 3 ? fmaf(a[k], bcast_scale, g[k]) : g[k] + a[k];
     }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      g[k] = fmaf(yy[k], ss[k].x, ss[k].y) > 0.f ? g[k] : 0.f;
-    }
+    for (int k = 0; k < 8; ++k) g[k] = fmaf(yy[k], ss[k].x, ss[k].y) > 0.f ? g[k] : 0.f;
     const BF8 packed = pack8(g);
     dm[m * c8 + cg] = packed;
     float gq[8];
@@ -257,7 +270,15 @@ __global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8*
       s1[k] += gq[k];
       s2[k] = fmaf(gq[k], yy[k], s2[k]);
     }
+  };
+  const long long step = (long long)gridDim.x * lanes;
+  long long m = (long long)blockIdx.x * lanes + pl;
+  for (; m + step < M; m += 2 * step) {   // two pixels in flight
+    const Px p0 = fetch(m), p1 = fetch(m + step);
+    finish(m, p0);
+    finish(m + step, p1);
   }
+  if (m < M) finish(m, fetch(m));
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     s_acc[threadIdx.x * 16 + k] = s1[k];
@@ -639,13 +660,19 @@ extern "C" int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int ad
               "bn_bwd_mask_reduce: phase-compact gradients need even H and W");
   DRN_REQUIRE(da != nullptr || addend_kind != 0, "bn_bwd_mask_reduce: no gradient given");
   const long long M = (long long)N * H * W;
+  DRN_REQUIRE(M < (1LL << 31), "bn_bwd_mask_reduce: more than 2^31 pixels");
   const int lanes = kThreads / (C / 8);
   long long blocks = (M + lanes - 1) / lanes;
-  const long long cap = (long long)num_sms() * 4;
+  const long long cap = (long long)num_sms() * 8;
   if (blocks > cap) blocks = cap;
-  DRN_CHECK_CUDA(launch_pdl(bn_bwd_mask_reduce_kernel, dim3((int)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
-                            (const BF8*)da, (const BF8*)addend, addend_kind, H, W, Ha, Wa, bcast_scale, (const BF8*)y,
-      (const float2*)scale_shift, (BF8*)dm, stats, stats_ld, M, C / 8));
+  auto kern = addend_kind == 0   ? bn_bwd_mask_reduce_kernel<0>
+              : addend_kind == 1 ? bn_bwd_mask_reduce_kernel<1>
+              : addend_kind == 2 ? bn_bwd_mask_reduce_kernel<2>
+              : addend_kind == 3 ? bn_bwd_mask_reduce_kernel<3>
+                                 : bn_bwd_mask_reduce_kernel<4>;
+  DRN_CHECK_CUDA(launch_pdl(kern, dim3((int)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)da, (const BF8*)addend, H, W, Ha, Wa, bcast_scale, (const BF8*)y,
+                            (const float2*)scale_shift, (BF8*)dm, stats, stats_ld, M, C / 8));
   return 0;
 }
 

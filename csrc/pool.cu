@@ -89,12 +89,14 @@ __global__ void maxpool3x3s2_fwd_kernel(const BF8* __restrict__ x, BF8* __restri
   const long long total = (long long)N * P * Q * c8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % c8);
-    long long t = i / c8;
-    const int q = (int)(t % Q);
-    t /= Q;
-    const int p = (int)(t % P);
-    const long long n = t / P;
+    // 32-bit index arithmetic (launcher checks the element count): 64-bit div/mod dominates otherwise
+    const unsigned iu = (unsigned)i;
+    const int cg = (int)(iu % (unsigned)c8);
+    unsigned t = iu / (unsigned)c8;
+    const int q = (int)(t % (unsigned)Q);
+    t /= (unsigned)Q;
+    const int p = (int)(t % (unsigned)P);
+    const long long n = t / (unsigned)P;
     const int h0 = p * 2 - pad_lo, w0 = q * 2 - pad_lo;
     BF8 v[9];
     bool ok[9];
@@ -190,12 +192,13 @@ __global__ void maxpool3x3s2_bwd_kernel(const BF8* __restrict__ dy, const U8x8* 
   const long long total = (long long)N * PI * QI * c8;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const int cg = (int)(idx % c8);
-    long long t = idx / c8;
-    const int j = (int)(t % QI);
-    t /= QI;
-    const int i = (int)(t % PI);
-    const long long n = t / PI;
+    const unsigned iu = (unsigned)idx;
+    const int cg = (int)(iu % (unsigned)c8);
+    unsigned t = iu / (unsigned)c8;
+    const int j = (int)(t % (unsigned)QI);
+    t /= (unsigned)QI;
+    const int i = (int)(t % (unsigned)PI);
+    const long long n = t / (unsigned)PI;
     float g[4][8];
 #pragma unroll
     for (int a = 0; a < 4; ++a)
@@ -290,7 +293,7 @@ extern "C" int drn_maxpool_fwd(const void* x, void* out, void* argmax, int N, in
   DRN_REQUIRE(C % 8 == 0, "maxpool: C must be a multiple of 8");
   DRN_REQUIRE(ksize * ksize < 255, "maxpool: window too large");
   const long long total = (long long)N * P * Q * (C / 8);
-  if (ksize == 3 && stride == 2) {
+  if (ksize == 3 && stride == 2 && total < (1LL << 31)) {
     DRN_CHECK_CUDA(launch_pdl(maxpool3x3s2_fwd_kernel, dim3(grid_for(total)), dim3(256), 0, (cudaStream_t)stream,
                             (const BF8*)x, (BF8*)out, (U8x8*)argmax, N, H, W, C / 8, P, Q, pad_lo));
     return 0;
@@ -307,6 +310,7 @@ extern "C" int drn_maxpool_bwd(const void* dy, const void* argmax, void* dx, int
   if (ksize == 3 && stride == 2 && pad_lo >= 0 && pad_lo <= 1) {
     const int PI = (H - 1 + pad_lo) / 2 + 1, QI = (W - 1 + pad_lo) / 2 + 1;
     const long long patches = (long long)N * PI * QI * (C / 8);
+    DRN_REQUIRE(patches < (1LL << 31), "maxpool_bwd: tensor too large for the 3x3/2 specialisation");
     DRN_CHECK_CUDA(launch_pdl(maxpool3x3s2_bwd_kernel, dim3(grid_for(patches)), dim3(256), 0, (cudaStream_t)stream,
                             (const BF8*)dy, (const U8x8*)argmax, (BF8*)dx, N, H, W, C / 8, P, Q, pad_lo, PI, QI));
     return 0;

@@ -38,6 +38,8 @@ WGRAD_SIDE_STREAM = os.environ.get("DRN_WGRAD_STREAM", "1") != "0"
 # first BatchNorm+ReLU of a bottleneck block applied inside its consumers (drn_conv_igemm_pre /
 # drn_conv_wgrad_pre) instead of being written to memory; DRN_FUSE_BN0=0 restores the separate pass
 FUSE_BN0 = os.environ.get("DRN_FUSE_BN0", "1") != "0"
+# data gradient of the strided 3x3 convolutions as four parity-phase convolutions (no zero insertion)
+DGRAD_S2_PHASES = os.environ.get("DRN_DGRAD_S2", "1") != "0"
 
 
 def _fuse_bn0(blk: BlockSpec) -> bool:
@@ -200,7 +202,8 @@ class _BN:
 
 
 class _Conv:
-    def __init__(self, spec: ConvSpec, eng: "NativeResNet", geom: ConvGeom, need_dgrad: bool):
+    def __init__(self, spec: ConvSpec, eng: "NativeResNet", geom: ConvGeom, need_dgrad: bool,
+                 s2_phases: bool = False):
         self.spec = spec
         self.g = geom
         self.desc = geom.desc()
@@ -210,11 +213,17 @@ class _Conv:
         self.wd = None
         self.dg = None
         self.up = None
+        self.wd_s2 = None
+        if (need_dgrad and s2_phases and DGRAD_S2_PHASES and geom.R == 3 and geom.S == 3 and geom.stride == 2
+                and (geom.pad_lo, geom.pad_hi) == (1, 1) and geom.H % 2 == 0 and geom.W % 2 == 0):
+            # four phase banks, see drn_conv_dgrad_s2; refreshed by prep_dgrad_weights()
+            self.wd_s2 = torch.empty(9 * geom.K * geom.C, dtype=torch.bfloat16, device=eng.device)
+            eng._s2_convs.append(self)
         if need_dgrad:
             self.wd = eng.alloc_dgrad_bank(name, geom.K * geom.R * geom.S * geom.C)
             self.dg = geom.dgrad_geom()
             self.dg_desc = self.dg.desc()
-            if geom.stride > 1 and geom.R > 1:
+            if geom.stride > 1 and geom.R > 1 and self.wd_s2 is None:
                 self.up = torch.zeros((geom.N, self.dg.H, self.dg.W, geom.K), dtype=torch.bfloat16,
                                       device=eng.device)
 
@@ -251,6 +260,7 @@ class NativeResNet:
         self._wd_arena = torch.zeros(self.layout.total + 64 * len(self.layout.order), dtype=torch.bfloat16, device=dev)
         self._wd_off = 0
         self._wd_entries: List[Tuple[str, int]] = []
+        self._s2_convs: List["_Conv"] = []
         m = self.layout.stem_mask()
         self.stem_mask = torch.from_numpy(m).to(dev).reshape(-1) if m is not None else None
         self._build()
@@ -368,7 +378,7 @@ class NativeResNet:
             sizes.append(d["shortcut"].numel())
         convs, bns, ys, acts = [], [], [], []
         for i, c in enumerate(blk.convs):
-            convs.append(_Conv(c, self, self._geom(c), need_dgrad=True))
+            convs.append(_Conv(c, self, self._geom(c), need_dgrad=True, s2_phases=i >= 1))
             last = i + 1 == len(blk.convs)
             y = self._act(B, c.hout, c.hout, c.cout)
             ys.append(y)
@@ -464,8 +474,11 @@ class NativeResNet:
         backward() waits for it."""
         if not hasattr(self, "_prep_table"):
             self._build_prep_table()
+        st = self._st() if stream_handle is None else stream_handle
         _nl.call("drn_weight_prep_dgrad_batched", _p(self.shadow), _p(self._wd_arena), _p(self._prep_table),
-                 self._prep_layers, self._prep_tiles, self._st() if stream_handle is None else stream_handle)
+                 self._prep_layers, self._prep_tiles, st)
+        for c in self._s2_convs:
+            _nl.call("drn_weight_prep_dgrad_s2", _p(c.w), _p(c.wd_s2), c.g.K, c.g.C, st)
 
     def _conv(self, desc, x, w, y, side=None, stats=None, ss=None, mode=EPI_PLAIN, pre=None):
         """``pre``: (scale, shift) table of a BatchNorm+ReLU to apply to ``x`` on the fly."""
@@ -744,7 +757,17 @@ class NativeResNet:
             y_prev, a_prev = ys[i - 1], acts[i - 1]
             self._wgrad(c, a_prev, dy, dy_i)
             dm_i, dm = self._get(y_prev)
-            self._dgrad(c, dy, dm, side=y_prev, stats=bn.bstats, ss=bn.ss, mode=EPI_BNBWD)
+            if c.wd_s2 is not None:
+                # strided 3x3: four parity-phase convolutions over dy, interleaved by the mask kernel
+                ph_i, ph = self._get(y_prev)
+                _nl.call("drn_conv_dgrad_s2", ctypes.byref(c.desc), _p(dy), _p(c.wd_s2), _p(ph), st)
+                _nl.add_launches(3)
+                Bn_, Hn_, Wn_, Cn_ = y_prev.shape
+                _nl.call("drn_bn_bwd_mask_reduce", _p(ph), 0, 4, Bn_, Hn_, Wn_, 0, 0, 0.0, _p(y_prev), _p(bn.ss),
+                         _p(dm), _p(bn.bstats), bn.bstats.stride(0), Cn_, st)
+                self._put(ph_i)
+            else:
+                self._dgrad(c, dy, dm, side=y_prev, stats=bn.bstats, ss=bn.ss, mode=EPI_BNBWD)
             if dy_i != g_i:
                 self._put(dy_i)
             n_i, ndy = self._get(y_prev)
