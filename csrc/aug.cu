@@ -161,6 +161,40 @@ __global__ void resize_bilinear_kernel(const uint8_t* __restrict__ src, int sh, 
   }
 }
 
+
+// Batched "VGG" resize + crop straight from the planar RGB output of a GPU JPEG decoder
+// (vgg_preprocessing.py:259-333): every output pixel of the 224x224 crop is sampled from the source
+// with TF1 resize_bilinear(align_corners=False) semantics (src = dst * in/out, no half-pixel
+// offset, edge clamp), rounded to the nearest grey level.  The resized image is never materialised.
+// meta[b] = {src_h, src_w, new_h, new_w, off_y, off_x}; src[b] -> uint8 [3][src_h][src_w].
+__global__ void resize_crop_batch_kernel(const uint8_t* const* __restrict__ src,
+                                         const int* __restrict__ meta, uint8_t* __restrict__ out,
+                                         int B, int crop) {
+  const int b = blockIdx.y;
+  const int sh = meta[b * 6 + 0], sw = meta[b * 6 + 1], nh = meta[b * 6 + 2], nw = meta[b * 6 + 3];
+  const int oy = meta[b * 6 + 4], ox = meta[b * 6 + 5];
+  const uint8_t* img = src[b];
+  const float scale_y = (float)sh / (float)nh, scale_x = (float)sw / (float)nw;
+  const long long plane = (long long)sh * sw;
+  uint8_t* dst = out + (long long)b * crop * crop * 3;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < crop * crop; i += gridDim.x * blockDim.x) {
+    const int x = i % crop, y = i / crop;
+    const float fy = (y + oy) * scale_y, fx = (x + ox) * scale_x;
+    const int y0 = min((int)floorf(fy), sh - 1), x0 = min((int)floorf(fx), sw - 1);
+    const int y1 = min(y0 + 1, sh - 1), x1 = min(x0 + 1, sw - 1);
+    const float ly = fy - (float)y0, lx = fx - (float)x0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const uint8_t* pl = img + c * plane;
+      const float tl = pl[(long long)y0 * sw + x0], tr = pl[(long long)y0 * sw + x1];
+      const float bl = pl[(long long)y1 * sw + x0], br = pl[(long long)y1 * sw + x1];
+      const float top = tl + (tr - tl) * lx, bot = bl + (br - bl) * lx;
+      const float v = top + (bot - top) * ly;
+      dst[i * 3 + c] = (uint8_t)fminf(fmaxf(rintf(v), 0.f), 255.f);
+    }
+  }
+}
+
 }  // namespace
 }  // namespace drn
 
@@ -200,6 +234,18 @@ extern "C" int drn_resize_bilinear(const void* src, int sh, int sw, float* dst, 
   const int total = dh * dw;
   resize_bilinear_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
       (const uint8_t*)src, sh, sw, dst, dh, dw, (float)sh / (float)dh, (float)sw / (float)dw);
+  DRN_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// src_ptrs: DEVICE array of B pointers to planar uint8 [3][h][w] images; meta: DEVICE int[B][6]
+// {src_h, src_w, new_h, new_w, off_y, off_x}; out: uint8 [B][crop][crop][3] (what drn_imagenet_prep reads).
+extern "C" int drn_resize_crop_batch(const void* src_ptrs, const int* meta, void* out, int B, int crop,
+                                     void* stream) {
+  DRN_REQUIRE(B > 0 && crop > 0, "resize_crop_batch: empty batch");
+  dim3 grid((crop * crop + 255) / 256 > 64 ? 64 : (crop * crop + 255) / 256, B);
+  resize_crop_batch_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const uint8_t* const*)src_ptrs, meta,
+                                                                   (uint8_t*)out, B, crop);
   DRN_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

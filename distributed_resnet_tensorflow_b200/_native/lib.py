@@ -45,6 +45,7 @@ _SIGNATURES = {
     "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
     "drn_conv_igemm_view": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
+    "drn_resize_crop_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "drn_weight_prep_dgrad_s2": (_i, [_vp, _vp, _i, _i, _vp]),
     "drn_conv_dgrad_s2": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp]),
     "drn_conv_wgrad_pre": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _i, _vp]),

@@ -105,3 +105,105 @@ class ImageNetBatches:
                 yield emit()
         if out:
             yield emit()
+
+
+def gpu_decode_available() -> bool:
+    """True when torchvision can decode JPEG batches on the GPU (nvJPEG)."""
+    try:
+        import torch
+        import torchvision  # noqa: F401
+        from torchvision.io import decode_jpeg  # noqa: F401
+        return torch.cuda.is_available()
+    except Exception:  # pragma: no cover - depends on the image
+        return False
+
+
+class ImageNetBatchesGPU(ImageNetBatches):
+    """Same stream of examples, but the pixels never touch the host: records are parsed on worker
+    threads (tf.Example only), a whole batch of JPEG byte strings is decoded by nvJPEG on the GPU
+    (``torchvision.io.decode_jpeg(..., device=...)``), and ONE launch of ``drn_resize_crop_batch``
+    produces the uint8 224x224 crops that ``drn_imagenet_prep`` consumes.  The reference decodes and
+    resizes on five CPU threads (resnet_imagenet_main.py:138-168) - a few hundred images per second,
+    against the >13 000 img/s a B200 trains at.
+
+    The shuffle buffer holds encoded examples (smaller than decoded crops).  Files nvJPEG rejects
+    (CMYK, the PNG hiding in the ImageNet train set) are decoded with PIL and uploaded.
+    Yields (images uint8 CUDA [B, 224*224*3], labels int32 [B], crop int32 [B,3] = (0,0,flip))."""
+
+    def __init__(self, data_dir: str, batch_size: int, training: bool, num_epochs: Optional[int] = None,
+                 seed: int = 0, num_threads: int = 5, files: Optional[List[str]] = None,
+                 device: str = "cuda:0", out_hw: int = 224):
+        super().__init__(data_dir, batch_size, training, num_epochs, seed, num_threads, files)
+        import torch
+        self.device = torch.device(device)
+        self.out_hw = out_hw
+
+    def _encoded(self) -> Iterator[Tuple[bytes, int, int]]:
+        """(jpeg bytes, label, per-example seed) in file order (shuffled shard list when training)."""
+        epoch = 0
+        while self.num_epochs is None or epoch < self.num_epochs:
+            files = list(self.files)
+            if self.training:
+                self.rng.shuffle(files)
+            for f in files:
+                for enc, lab in self.pool.map(parse_record, read_tfrecords(f)):
+                    yield enc, lab, int(self.rng.integers(0, 2 ** 31))
+            epoch += 1
+
+    def _decode_batch(self, items):
+        import torch
+        from torchvision.io import ImageReadMode, decode_jpeg
+        from .._native import lib as _nl
+        B = len(items)
+        bufs = [torch.frombuffer(bytearray(enc), dtype=torch.uint8) for enc, _, _ in items]
+        try:
+            imgs = decode_jpeg(bufs, device=self.device, mode=ImageReadMode.RGB)
+        except Exception:
+            imgs = []
+            for (enc, _, _), b in zip(items, bufs):
+                try:
+                    imgs.append(decode_jpeg(b, device=self.device, mode=ImageReadMode.RGB))
+                except Exception:   # not a baseline/progressive RGB or grey JPEG: host decoder
+                    imgs.append(torch.from_numpy(decode_image(enc)).permute(2, 0, 1).contiguous().to(self.device))
+        imgs = [im.contiguous() for im in imgs]
+        meta = np.zeros((B, 6), np.int32)
+        flips = np.zeros(B, np.int32)
+        for i, ((_, _, seed), im) in enumerate(zip(items, imgs)):
+            h, w = int(im.shape[1]), int(im.shape[2])
+            nh, nw, oy, ox, flip = preprocess.vgg_crop_params(h, w, self.training, self.out_hw,
+                                                              np.random.default_rng(seed))
+            meta[i] = (h, w, nh, nw, oy, ox)
+            flips[i] = flip
+        ptrs = torch.tensor([im.data_ptr() for im in imgs], dtype=torch.int64).to(self.device)
+        dmeta = torch.from_numpy(meta).to(self.device)
+        out = torch.empty((B, self.out_hw * self.out_hw * 3), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            _nl.call("drn_resize_crop_batch", ptrs.data_ptr(), dmeta.data_ptr(), out.data_ptr(), B, self.out_hw,
+                     torch.cuda.current_stream().cuda_stream)
+            torch.cuda.current_stream().synchronize()   # `imgs` may be freed; consumers use other streams
+        labs = np.asarray([lab for _, lab, _ in items], np.int32)
+        crop = np.stack([np.zeros(B, np.int32), np.zeros(B, np.int32), flips], 1).astype(np.int32)
+        return out, labs, crop
+
+    def __iter__(self):
+        buf: List[Tuple[bytes, int, int]] = []
+        out: List[Tuple[bytes, int, int]] = []
+        cap = SHUFFLE_BUFFER if self.training else 1
+        for ex in self._encoded():
+            buf.append(ex)
+            if len(buf) >= cap:
+                i = int(self.rng.integers(0, len(buf))) if self.training else 0
+                buf[i], buf[-1] = buf[-1], buf[i]
+                out.append(buf.pop())
+                if len(out) == self.B:
+                    yield self._decode_batch(out)
+                    out = []
+        if self.training:
+            self.rng.shuffle(buf)
+        for ex in buf:
+            out.append(ex)
+            if len(out) == self.B:
+                yield self._decode_batch(out)
+                out = []
+        if out:
+            yield self._decode_batch(out)

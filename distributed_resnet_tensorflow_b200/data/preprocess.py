@@ -126,6 +126,23 @@ def vgg_preprocess(img01: np.ndarray, training: bool, out_hw: int = 224,
     return (img - VGG_MEANS_01).astype(np.float32)
 
 
+def vgg_crop_params(h: int, w: int, training: bool, out_hw: int = 224,
+                    rng: np.random.Generator = None) -> Tuple[int, int, int, int, int]:
+    """(new_h, new_w, off_y, off_x, flip) of the reference's VGG preprocessing for an h x w image
+    (vgg_preprocessing.py:284-333): training = random short side in [256, 512], random crop, random
+    flip; evaluation = short side 256, central crop.  Shared by the host and the GPU input paths so
+    that both make identical decisions from the same generator."""
+    if training:
+        rng = rng or np.random.default_rng()
+        side = int(rng.integers(RESIZE_SIDE_MIN, RESIZE_SIDE_MAX + 1))
+        nh, nw = smallest_size_at_least(h, w, side)
+        oy = int(rng.integers(0, nh - out_hw + 1))
+        ox = int(rng.integers(0, nw - out_hw + 1))
+        return nh, nw, oy, ox, int(rng.integers(0, 2))
+    nh, nw = smallest_size_at_least(h, w, RESIZE_SIDE_MIN)
+    return nh, nw, (nh - out_hw) // 2, (nw - out_hw) // 2, 0
+
+
 def vgg_resize_crop_u8(img_u8: np.ndarray, training: bool, out_hw: int = 224,
                        rng: np.random.Generator = None) -> Tuple[np.ndarray, int]:
     """Host half of the device pipeline: decoded uint8 HWC -> resized + cropped uint8 [hw, hw, 3]
@@ -133,19 +150,8 @@ def vgg_resize_crop_u8(img_u8: np.ndarray, training: bool, out_hw: int = 224,
     layout happen in drn_imagenet_prep.  Quantising the resized image back to uint8 loses at most
     half a grey level (1/510) relative to the reference's float pipeline."""
     h, w = img_u8.shape[:2]
-    if training:
-        rng = rng or np.random.default_rng()
-        side = int(rng.integers(RESIZE_SIDE_MIN, RESIZE_SIDE_MAX + 1))
-        nh, nw = smallest_size_at_least(h, w, side)
-        img = resize_bilinear(img_u8, nh, nw)
-        oy = int(rng.integers(0, nh - out_hw + 1))
-        ox = int(rng.integers(0, nw - out_hw + 1))
-        img = img[oy:oy + out_hw, ox:ox + out_hw]
-        flip = int(rng.integers(0, 2))
-    else:
-        nh, nw = smallest_size_at_least(h, w, RESIZE_SIDE_MIN)
-        img = central_crop(resize_bilinear(img_u8, nh, nw), out_hw, out_hw)
-        flip = 0
+    nh, nw, oy, ox, flip = vgg_crop_params(h, w, training, out_hw, rng)
+    img = resize_bilinear(img_u8, nh, nw)[oy:oy + out_hw, ox:ox + out_hw]
     return np.clip(np.rint(img), 0, 255).astype(np.uint8), flip
 
 

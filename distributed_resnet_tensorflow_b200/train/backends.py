@@ -247,6 +247,12 @@ class NativeBackend:
         return self.trainer.global_step
 
     def _stage(self, images_u8, labels, crop):
+        if isinstance(images_u8, torch.Tensor) and images_u8.is_cuda:
+            # batch produced on the device (GPU JPEG decode): no pinned bounce for the pixels
+            self._pin_l.copy_(torch.from_numpy(np.asarray(labels, np.int32)))
+            if crop is not None:
+                self._pin_c.copy_(torch.from_numpy(np.asarray(crop, np.int32)))
+            return images_u8.view(self.B, -1), self._pin_l, (self._pin_c if self.spec.dataset == "imagenet" else None)
         self._pin_i.copy_(torch.from_numpy(np.ascontiguousarray(images_u8).reshape(self.B, -1)))
         self._pin_l.copy_(torch.from_numpy(np.asarray(labels, np.int32)))
         if crop is not None:

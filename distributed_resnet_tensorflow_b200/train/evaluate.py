@@ -27,12 +27,17 @@ from .loop import choose_backend, local_device
 log = logging.getLogger("drn")
 
 
-def eval_batches(cfg: Config, spec, batch: int) -> Iterator[Tuple]:
+def eval_batches(cfg: Config, spec, batch: int, device: Optional[str] = None) -> Iterator[Tuple]:
     if spec.dataset == "imagenet":
         if cfg.paths.eval_data_path and not cfg.train.synthetic_data:
-            from ..data.imagenet import ImageNetBatches
+            from ..data.imagenet import ImageNetBatches, ImageNetBatchesGPU
+            from .loop import use_gpu_decode
+            gpu = use_gpu_decode(cfg, device)
             while True:
-                yield from ImageNetBatches(cfg.paths.eval_data_path, batch, False, 1)
+                if gpu:
+                    yield from ImageNetBatchesGPU(cfg.paths.eval_data_path, batch, False, 1, device=device)
+                else:
+                    yield from ImageNetBatches(cfg.paths.eval_data_path, batch, False, 1)
         from ..data.synthetic import synthetic_imagenet_batches
         for imgs, labs in synthetic_imagenet_batches(batch, spec.num_classes, spec.image_size, 99):
             yield imgs, labs, np.zeros((batch, 3), np.int32)
@@ -63,7 +68,7 @@ def evaluate(cfg: Config, max_rounds: Optional[int] = None) -> Dict[str, float]:
                           weight_decay=cfg.train.weight_decay)
     names = [n for n, _ in spec.trainable_variables()] + [n for n, _ in spec.moving_variables()] + ["global_step"]
     writer = EventFileWriter(cfg.paths.eval_dir) if cfg.paths.eval_dir else None
-    batches = eval_batches(cfg, spec, B)
+    batches = eval_batches(cfg, spec, B, device if backend_name == "native" else None)
     best_precision, last_path, rounds = 0.0, None, 0
     result: Dict[str, float] = {}
     while True:

@@ -83,12 +83,28 @@ def init_process_group(cfg: Config, ctx: DistContext, device_type: str) -> None:
 # ------------------------------------------------------------------------------------------------
 # data
 # ------------------------------------------------------------------------------------------------
-def training_batches(cfg: Config, spec: NetSpec, ctx: DistContext) -> Iterator[Tuple]:
+def use_gpu_decode(cfg: Config, device: Optional[str]) -> bool:
+    """--input_decode: gpu needs a CUDA device and torchvision's nvJPEG binding; auto picks it when
+    the step itself runs on the GPU."""
+    mode = cfg.train.input_decode
+    if mode == "cpu" or device is None or not str(device).startswith("cuda"):
+        return False
+    from ..data.imagenet import gpu_decode_available
+    ok = gpu_decode_available()
+    if mode == "gpu" and not ok:
+        raise RuntimeError("--input_decode=gpu needs torchvision with CUDA JPEG decoding")
+    return ok
+
+
+def training_batches(cfg: Config, spec: NetSpec, ctx: DistContext, device: Optional[str] = None) -> Iterator[Tuple]:
     B = cfg.train.batch_size
     seed = cfg.train.seed + 1000 * max(ctx.worker_index, 0)  # replicas shuffle independently
     if spec.dataset == "imagenet":
         if cfg.paths.train_data_path and not cfg.train.synthetic_data:
-            from ..data.imagenet import ImageNetBatches
+            from ..data.imagenet import ImageNetBatches, ImageNetBatchesGPU
+            if use_gpu_decode(cfg, device):
+                return iter(ImageNetBatchesGPU(cfg.paths.train_data_path, B, True, cfg.train.num_epochs, seed,
+                                               device=device))
             return iter(ImageNetBatches(cfg.paths.train_data_path, B, True, cfg.train.num_epochs, seed))
         from ..data.synthetic import synthetic_imagenet_batches
 
@@ -228,7 +244,7 @@ def train(cfg: Config) -> Dict[str, float]:
     saver = Saver(cfg.paths.log_root, t.keep_checkpoint_max) if (cfg.paths.log_root and ctx.is_chief) else None
     summary_dir = cfg.paths.train_dir if cfg.model.dataset == "imagenet" else (cfg.paths.eval_dir or cfg.paths.train_dir)
     writer = EventFileWriter(summary_dir) if (ctx.is_chief and summary_dir) else None
-    batches = training_batches(cfg, spec, ctx)
+    batches = training_batches(cfg, spec, ctx, device if backend_name == "native" else None)
     start_step = be.global_step
     t_log, s_log = time.time(), start_step
     metrics: Dict[str, float] = {}

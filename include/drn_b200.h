@@ -216,6 +216,11 @@ int drn_imagenet_prep(const void* src, long long image_stride, int src_h, int sr
                       const int* crop_yx_flip, void* out, int B, int crop, float mean_r,
                       float mean_g, float mean_b, int out_pitch, int out_xoff, void* stream);
 int drn_resize_bilinear(const void* src, int sh, int sw, float* dst, int dh, int dw, void* stream);
+/* Batched aspect-preserving resize (TF1 bilinear, align_corners=False) + crop directly from the planar
+ * RGB output of a GPU JPEG decoder: src_ptrs = DEVICE array of B pointers to uint8 [3][h][w];
+ * meta = DEVICE int[B][6] {src_h, src_w, new_h, new_w, off_y, off_x}; out = uint8 [B][crop][crop][3]. */
+int drn_resize_crop_batch(const void* src_ptrs, const int* meta, void* out, int B, int crop,
+                          void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Host utilities (no GPU): CRC-32C (Castagnoli) used by TensorBundle checkpoints, TFRecord files

@@ -49,3 +49,40 @@ def test_imagenet_main_serial_native(tmp_path):
     out = _run([os.path.join(ROOT, "resnet_imagenet_main.py"), "--resnet_size=18", "--batch_size=16", "--num_gpus=1",
                 "--train_steps=12", "--log_every=4", f"--log_root={tmp_path / 'ckpt'}", f"--train_dir={tmp_path / 'tr'}"])
     assert "backend=native" in out and "step = 12" in out
+
+
+def test_gpu_jpeg_input_path_matches_the_host_path(tmp_path):
+    """TFRecord shards of synthetic JPEGs through both ImageNet input paths: PIL decode + numpy
+    resize/crop on the host vs nvJPEG batch decode + drn_resize_crop_batch on the device.  Both
+    draw the same crop decisions; the decoders may differ by a grey level or two."""
+    import io
+    import numpy as np
+    import torch
+    from PIL import Image
+    from distributed_resnet_tensorflow_b200.data import imagenet as im
+    from distributed_resnet_tensorflow_b200.data.tfrecord import make_example, write_tfrecords
+    if not im.gpu_decode_available():
+        pytest.skip("torchvision GPU JPEG decode not available")
+    rng = np.random.default_rng(0)
+    records = []
+    for i in range(12):
+        h, w = int(rng.integers(260, 420)), int(rng.integers(260, 520))
+        yy, xx = np.mgrid[0:h, 0:w]
+        img = np.stack([(yy * 255 // h), (xx * 255 // w), ((yy + xx) * 255 // (h + w))], 2).astype(np.uint8)
+        img = (img.astype(np.int32) + rng.integers(-6, 7, img.shape)).clip(0, 255).astype(np.uint8)
+        if i == 5:
+            img = img[:, :, 0]            # one greyscale JPEG, as ImageNet has
+        buf = io.BytesIO()
+        Image.fromarray(img).save(buf, format="JPEG", quality=92)
+        records.append(make_example({"image/encoded": [buf.getvalue()], "image/class/label": [i + 1]}))
+    shard = str(tmp_path / "validation-00000-of-00128")
+    write_tfrecords(shard, records)
+    for training in (False, True):
+        host = list(im.ImageNetBatches(str(tmp_path), 4, training, 1, seed=3, files=[shard]))
+        dev = list(im.ImageNetBatchesGPU(str(tmp_path), 4, training, 1, seed=3, files=[shard], device="cuda:0"))
+        assert len(host) == len(dev) == 3
+        for (hi, hl, hc), (di, dl, dc) in zip(host, dev):
+            assert di.is_cuda and di.dtype == torch.uint8 and tuple(di.shape) == hi.shape
+            assert np.array_equal(hl, dl) and np.array_equal(hc, dc)
+            diff = np.abs(di.cpu().numpy().astype(np.int32) - hi.astype(np.int32))
+            assert diff.mean() < 1.5 and np.percentile(diff, 99) <= 8, (diff.mean(), diff.max())
