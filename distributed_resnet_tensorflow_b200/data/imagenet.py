@@ -123,8 +123,10 @@ class ImageNetBatchesGPU(ImageNetBatches):
     threads (tf.Example only), a whole batch of JPEG byte strings is decoded by nvJPEG on the GPU
     (``torchvision.io.decode_jpeg(..., device=...)``), and ONE launch of ``drn_resize_crop_batch``
     produces the uint8 224x224 crops that ``drn_imagenet_prep`` consumes.  The reference decodes and
-    resizes on five CPU threads (resnet_imagenet_main.py:138-168) - a few hundred images per second,
-    against the >13 000 img/s a B200 trains at.
+    resizes on five CPU threads (resnet_imagenet_main.py:138-168).  Measured (bench/bench_input.py):
+    both paths deliver ~1 000 images/s per process - torchvision's binding still Huffman-decodes on
+    the host - so this path buys CPU threads, not throughput; a B200 trains at >13 000 img/s, so real
+    data needs either many ranks' worth of cores or the nvJPEG hardware backend (not wired up).
 
     The shuffle buffer holds encoded examples (smaller than decoded crops).  Files nvJPEG rejects
     (CMYK, the PNG hiding in the ImageNet train set) are decoded with PIL and uploaded.

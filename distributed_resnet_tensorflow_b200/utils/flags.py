@@ -255,7 +255,7 @@ EXTENSION_FLAGS: List[FlagDef] = [
     _n("seed", 0, "Base RNG seed (initialisation is identical on all replicas)."),
     _b("synthetic_data", False, "Force synthetic inputs even if a data path is given."),
     _s("input_decode", "auto", "ImageNet JPEG decode + resize: cpu (PIL worker threads, as the reference), "
-       "gpu (nvJPEG batch decode + one resize/crop kernel), auto = gpu with the native backend."),
+       "gpu (nvJPEG batch decode + one resize/crop kernel, frees the CPU threads), auto = cpu."),
     _b("profile", False, "Print the parameter / FLOP table (tfprof-style) and per-kernel timings."),
     _b("cuda_graph", True, "Capture the training step in a CUDA graph (native backend)."),
     _s("allreduce_algo", "auto", "auto | oneshot | twoshot | nccl."),
