@@ -522,6 +522,11 @@ class NativeResNet:
         if dy_idx is not None:
             self._buf_event[dy_idx] = done
 
+    def last_wgrad_event(self):
+        """Event recorded behind the most recent filter-gradient launch (None when everything runs on
+        one stream); a consumer of the gradient arena on another stream waits on it."""
+        return self._wg_last
+
     def _join_wgrads(self) -> None:
         if self._wg_last is not None:
             torch.cuda.current_stream().wait_event(self._wg_last)
@@ -708,13 +713,12 @@ class NativeResNet:
         g_i, g = self._get(x)
         self._bn_bwd(fb, dm, x, None, g)
         self._put(dm_i)
+        # the hooks order their consumer behind last_wgrad_event() themselves: no join here
         if range_hook is not None:
-            self._join_wgrads()
             range_hook(marks[-2], marks[-1], False)
         for bi in range(len(self.blocks) - 1, -1, -1):
             g_i, g = self._block_bwd(self.blocks[bi], g_i, g)
             if range_hook is not None:
-                self._join_wgrads()
                 range_hook(marks[bi + 1], marks[bi + 2], False)
         # stem
         if s.maxpool:

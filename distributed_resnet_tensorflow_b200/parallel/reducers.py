@@ -118,6 +118,11 @@ class AllreduceReducer(_ReducerBase):
             ev = self._event()
             ev.record(cur)
             cs.wait_event(ev)
+            # the filter gradients of this range run on the engine's second stream: the bucket waits
+            # for them here, the dependent chain on `cur` never does
+            wg = engine.last_wgrad_event()
+            if wg is not None:
+                cs.wait_event(wg)
             with torch.cuda.stream(cs):
                 st = cs.cuda_stream
                 if not skip:
@@ -149,6 +154,11 @@ class ParameterServerReducer(_ReducerBase):
             ev = self._event()
             ev.record(cur)
             cs.wait_event(ev)
+            # the filter gradients of this range run on the engine's second stream: the bucket waits
+            # for them here, the dependent chain on `cur` never does
+            wg = engine.last_wgrad_event()
+            if wg is not None:
+                cs.wait_event(wg)
             with torch.cuda.stream(cs):
                 _nl.call("drn_ps_update", self.grad_buf.ptr_array(), self.shadow_buf.ptr_array(),
                          _p(engine.master), _p(engine.mom), _p(engine.hyper), self.rank,
