@@ -63,10 +63,11 @@ constexpr int kPreThreads = 128;    // warps 12-15 of the PRE variant
 constexpr int kMaxRes = 8;          // side-input ring depth per epilogue group (upper bound)
 constexpr int kSmemBudget = 226 * 1024;
 
-template <int KC, int BN>
+template <int KC, int BN, bool TWO = false>
 struct Cfg {
   static constexpr int kABytes = kBM * KC * 2;
-  static constexpr int kBBytesRaw = BN * KC * 2;
+  static constexpr int kBRows = TWO ? BN / 2 : BN;     // CTA-pair: each CTA stages half of the B tile
+  static constexpr int kBBytesRaw = kBRows * KC * 2;
   static constexpr int kBBytes = (kBBytesRaw + 1023) / 1024 * 1024;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kCW = BN < 32 ? BN : 32;       // epilogue chunk width (columns)
@@ -91,15 +92,22 @@ struct Cfg {
   }
 };
 
-template <int KC, int BN, bool PRE = false>
+template <int KC, int BN, bool PRE = false, bool TWO = false>
 __global__ void __launch_bounds__(PRE ? kNumThreads + kPreThreads : kNumThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                   const __grid_constant__ CUtensorMap tmapC, const __grid_constant__ CUtensorMap tmapR,
                   const ConvParams p) {
-  using C_ = Cfg<KC, BN>;
+  using C_ = Cfg<KC, BN, TWO>;
+  static_assert(!(PRE && TWO), "the BatchNorm prologue has no CTA-pair variant");
   const int kStages = p.n_stages;
   constexpr int kCW = C_::kCW;
   constexpr int kRowBytes = C_::kRowBytes;
+  // CTA pair (TWO): the two CTAs of a (2,1,1) cluster own the row tiles 2*m_pair and 2*m_pair+1 of
+  // the same column tile; rank 0 issues ONE 256-row tcgen05.mma.cta_group::2 per k-step that reads
+  // both CTAs' A tiles and both halves of the B tile, so the weights cross the L2 fabric once per
+  // pair instead of once per CTA.  p.m_tiles then counts row-tile PAIRS.
+  const uint32_t cta_rank = TWO ? cluster_ctarank() : 0u;
+  const bool leader_cta = cta_rank == 0;
 
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment: required by the 128B swizzle atom (8 rows x 128 B).
@@ -129,9 +137,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 
   // Each CTA owns a contiguous range of the n-major tile order, so it crosses a column-tile
   // boundary (statistics flush, scale/shift reload) at most once or twice.
-  const int t_q = p.total_tiles / (int)gridDim.x, t_r = p.total_tiles % (int)gridDim.x;
-  const int t_begin = (int)blockIdx.x * t_q + ((int)blockIdx.x < t_r ? (int)blockIdx.x : t_r);
-  const int t_end = t_begin + t_q + ((int)blockIdx.x < t_r ? 1 : 0);
+  const int n_units = TWO ? (int)gridDim.x / 2 : (int)gridDim.x;   // CTAs, or CTA pairs
+  const int unit = TWO ? (int)blockIdx.x / 2 : (int)blockIdx.x;
+  const int t_q = p.total_tiles / n_units, t_r = p.total_tiles % n_units;
+  const int t_begin = unit * t_q + (unit < t_r ? unit : t_r);
+  const int t_end = t_begin + t_q + (unit < t_r ? 1 : 0);
+  // row tile of this CTA for the scheduler's tile index
+  auto row_tile = [&](int m_idx) { return TWO ? 2 * m_idx + (int)cta_rank : m_idx; };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmapA);
@@ -146,7 +158,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(tfull_bar(b), 1);
-      mbar_init(tempty_bar(b), kEpiThreads * C_::kChunks);  // one arrival per thread per chunk
+      // one arrival per thread per chunk (from both CTAs of a pair: the leader's barrier gates the MMA)
+      mbar_init(tempty_bar(b), TWO ? 2 * (kEpiThreads / 32) * C_::kChunks : kEpiThreads * C_::kChunks);
     }
     for (int b = 0; b < 2 * kMaxRes; ++b) mbar_init(res_bar(b), 1);
     if (PRE)
@@ -154,11 +167,17 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     fence_mbar_init();
   }
   if (warp == 2) {
-    tmem_alloc(sTmemPtr, C_::kTmemCols);
-    tmem_relinquish();
+    if (TWO) {
+      tmem_alloc_2cta(sTmemPtr, C_::kTmemCols);
+      tmem_relinquish_2cta();
+    } else {
+      tmem_alloc(sTmemPtr, C_::kTmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (TWO) cluster_sync_all();   // the peer's barriers must be initialised before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
   // everything above (barriers, TMEM, descriptor prefetch) overlapped the previous kernel's tail
@@ -171,7 +190,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
       uint32_t phase = 0;
       for (int t = t_begin; t < t_end; ++t) {
         const int n_tile = t / p.m_tiles;
-        const int m_tile = t - n_tile * p.m_tiles;
+        const int m_tile = row_tile(t - n_tile * p.m_tiles);
         const int m0 = m_tile * kBM;
         const int img = m0 / p.PQ;
         const int rem = m0 - img * p.PQ;
@@ -187,10 +206,19 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           mbar_wait_sleep(empty_bar(stage), phase ^ 1, 0x10 + stage, p.spin_ns);
           const uint32_t a_dst = sStages + stage * C_::kStageBytes;
           const uint32_t b_dst = a_dst + C_::kABytes;
-          mbar_arrive_expect_tx(full_bar(stage), C_::kABytes + C_::kBBytesRaw);
-          tma_load_im2col_4d(a_dst, &tmapA, full_bar(stage), cb * KC, w0, h0, img,
-                             static_cast<uint16_t>(s), static_cast<uint16_t>(r));
-          tma_load_2d(b_dst, &tmapB, full_bar(stage), tap * p.C + cb * KC, n_tile * BN);
+          if (TWO) {
+            // both CTAs load (own A rows, own half of B); all bytes are counted on the leader's barrier
+            if (leader_cta) mbar_arrive_expect_tx(full_bar(stage), 2 * (C_::kABytes + C_::kBBytesRaw));
+            tma_load_im2col_4d_2cta(a_dst, &tmapA, full_bar(stage), cb * KC, w0, h0, img,
+                                    static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+            tma_load_2d_2cta(b_dst, &tmapB, full_bar(stage), tap * p.C + cb * KC,
+                             n_tile * BN + (int)cta_rank * C_::kBRows);
+          } else {
+            mbar_arrive_expect_tx(full_bar(stage), C_::kABytes + C_::kBBytesRaw);
+            tma_load_im2col_4d(a_dst, &tmapA, full_bar(stage), cb * KC, w0, h0, img,
+                               static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+            tma_load_2d(b_dst, &tmapB, full_bar(stage), tap * p.C + cb * KC, n_tile * BN);
+          }
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
@@ -200,8 +228,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     }
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
-    if (elect_one()) {
-      constexpr uint32_t kIdesc = make_idesc_bf16(kBM, BN, 0, 0);
+    if (leader_cta && elect_one()) {
+      constexpr uint32_t kIdesc = make_idesc_bf16(TWO ? 2 * kBM : kBM, BN, 0, 0);
       constexpr uint32_t kLayout = umma_layout_for_swizzle_bytes(KC * 2);
       constexpr uint32_t kSBO = 8 * KC * 2;  // 8-row group stride (K-major, dense rows)
       int stage = 0;
@@ -222,15 +250,18 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 #pragma unroll
           for (int kk = 0; kk < KC / 16; ++kk) {
             // advance 16 elements (32 B) along K inside the swizzle span: +2 in (addr >> 4) units
-            umma_f16(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (it | kk) != 0 ? 1u : 0u);
+            if (TWO) umma_f16_2cta(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (it | kk) != 0 ? 1u : 0u);
+            else umma_f16(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (it | kk) != 0 ? 1u : 0u);
           }
-          umma_commit(empty_bar(stage));
+          if (TWO) umma_commit_2cta(empty_bar(stage), 3);   // frees the stage in both CTAs
+          else umma_commit(empty_bar(stage));
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(tfull_bar(acc));
+        if (TWO) umma_commit_2cta(tfull_bar(acc), 3);       // both epilogues may drain their 128 rows
+        else umma_commit(tfull_bar(acc));
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
@@ -376,7 +407,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
       locate(idx, tile, chunk);
       if (tile >= t_end) return;
       const int n_tile = tile / p.m_tiles;
-      const int m_tile = tile - n_tile * p.m_tiles;
+      const int m_tile = row_tile(tile - n_tile * p.m_tiles);
       const uint32_t b = idx % n_res;
       mbar_arrive_expect_tx(res_bar(grp * kMaxRes + b), C_::kChunkBytes);
       tma_load_2d(res_base + b * C_::kChunkBytes, &tmapR, res_bar(grp * kMaxRes + b),
@@ -396,7 +427,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
       const bool my_tile = C_::kChunks >= 2 || (tile_iter & 1) == grp;
       if (my_tile) {
         const int n_tile = t / p.m_tiles;
-        const int m_tile = t - n_tile * p.m_tiles;
+        const int m_tile = row_tile(t - n_tile * p.m_tiles);
         if (n_tile != cur_n_tile) {
           flush_stats(cur_n_tile);
           cur_n_tile = n_tile;
@@ -443,7 +474,16 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           }
           // every chunk's 128 threads arrive once: the buffer is free after kChunks*128 arrivals
           tc_fence_before();
-          mbar_arrive(tempty_bar(acc));
+          if (TWO) {
+            // one (possibly remote) arrival per warp: every lane has finished its tcgen05.ld
+            __syncwarp();
+            if (lane == 0) {
+              if (leader_cta) mbar_arrive(tempty_bar(acc));
+              else mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
+            }
+          } else {
+            mbar_arrive(tempty_bar(acc));
+          }
 
           if (has_res) {
             mbar_wait_sleep(res_bar(grp * kMaxRes + rb), (mine / n_res) & 1, 0x50 + grp * kMaxRes + rb, p.spin_ns);
@@ -539,10 +579,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (TWO) cluster_sync_all();   // the leader's MMAs read the peer's shared memory until the very end
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, C_::kTmemCols);
+    if (TWO) tmem_dealloc_2cta(tmem_base, C_::kTmemCols);
+    else tmem_dealloc(tmem_base, C_::kTmemCols);
   }
 }
 
@@ -551,15 +593,16 @@ inline int env_int(const char* name, int dflt) {
   return v ? atoi(v) : dflt;
 }
 
-template <int KC, int BN>
+template <int KC, int BN, bool TWO = false>
 int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, const void* side,
                 float* stats, int stats_ld, const void* bn_scale_shift, int mode,
                 cudaStream_t stream) {
-  using C_ = Cfg<KC, BN>;
+  using C_ = Cfg<KC, BN, TWO>;
   const int P = d.P, Q = d.Q;
   const long long M = 1LL * d.N * P * Q;
   ConvParams p;
   p.m_tiles = (int)((M + kBM - 1) / kBM);
+  if (TWO) p.m_tiles = (p.m_tiles + 1) / 2;   // row-tile pairs (an odd last tile pairs with an empty one)
   p.n_tiles = (d.K + BN - 1) / BN;
   p.total_tiles = p.m_tiles * p.n_tiles;
   p.c_blocks = d.C / KC;
@@ -596,7 +639,7 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
                                kBM, KC * 2, view ? vstr : nullptr))
     return e;
   if (int e = tmap_tiled_2d(&tB, w, 2, d.K, (uint64_t)d.R * d.S * d.C, (uint64_t)d.R * d.S * d.C,
-                            BN, KC, KC * 2))
+                            C_::kBRows, KC, KC * 2))
     return e;
   if (int e = tmap_tiled_2d(&tC, y, 2, (uint64_t)M, d.K, d.K, kBM, C_::kCW, C_::kRowBytes)) return e;
   if (mode != DRN_EPI_PLAIN) {
@@ -610,6 +653,20 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   p.pre_ss = reinterpret_cast<const float2*>(current_pre());
   p.M = M;
   p.spin_ns = (unsigned)env_int("DRN_SPIN_NS", 0);
+  if constexpr (TWO) {
+    DRN_REQUIRE(p.pre_ss == nullptr, "conv_igemm: no CTA-pair variant of the BatchNorm prologue");
+    const int pairs = num_sms() / 2;
+    grid = 2 * (p.total_tiles < pairs ? p.total_tiles : pairs);
+    static bool attr_set_two = false;
+    if (!attr_set_two) {
+      DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN, false, true>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
+      attr_set_two = true;
+    }
+    DRN_CHECK_CUDA(launch_cluster2(conv_igemm_kernel<KC, BN, false, true>, dim3(grid), dim3(kNumThreads),
+                                   smem_bytes, stream, tA, tB, tC, tR, p));
+    return 0;
+  }
   if (p.pre_ss != nullptr) {
     if constexpr (KC == 64 && (BN == 64 || BN == 128)) {
       DRN_REQUIRE(d.R == 1 && d.S == 1 && d.pad_lo == 0 && d.pad_hi == 0 && view == nullptr,
@@ -641,7 +698,11 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
 template <int KC>
 int dispatch_bn(int bn, const drn_conv_desc& d, const void* x, const void* w, void* y,
                 const void* side, float* stats, int stats_ld, const void* ss, int mode,
-                cudaStream_t st) {
+                cudaStream_t st, bool two = false) {
+  if constexpr (KC == 64) {
+    if (two && bn == 128) return launch_conv<KC, 128, true>(d, x, w, y, side, stats, stats_ld, ss, mode, st);
+    if (two && bn == 256) return launch_conv<KC, 256, true>(d, x, w, y, side, stats, stats_ld, ss, mode, st);
+  }
   switch (bn) {
     case 16: return launch_conv<KC, 16>(d, x, w, y, side, stats, stats_ld, ss, mode, st);
     case 32: return launch_conv<KC, 32>(d, x, w, y, side, stats, stats_ld, ss, mode, st);
@@ -695,7 +756,16 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
   switch (kc) {
     case 16: return dispatch_bn<16>(bn, d, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, st);
     case 32: return dispatch_bn<32>(bn, d, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, st);
-    default: return dispatch_bn<64>(bn, d, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, st);
+    default: {
+      // CTA pairs (DRN_TWO_CTA: 0 never, 1 policy, 2 always where a variant exists).  Measured
+      // (bench/check_two.py): halving the weight traffic pays only where the weights dominate the
+      // L2->SM stream - 3x3 over 512 channels at 7x7, 47 -> 41 us; everywhere else the pair's
+      // lock-step costs as much as it saves (or more: 1x1 256->1024 at 14x14, 46 -> 66 us).
+      const int two_env = env_int("DRN_TWO_CTA", 1);
+      const bool two = current_pre() == nullptr && current_view() == nullptr && (bn == 128 || bn == 256) &&
+                       two_env >= 1 && (two_env >= 2 || d.R * d.S * d.C >= 4096);
+      return dispatch_bn<64>(bn, d, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, st, two);
+    }
   }
 }
 

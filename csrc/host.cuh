@@ -54,6 +54,24 @@ inline cudaError_t launch_pdl_kind(int kind_bit, void (*kernel)(KArgs...), dim3 
   cfg.numAttrs = (pdl_mask() & kind_bit) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
+// Launch with a (2,1,1) thread-block cluster (CTA pairs for tcgen05 cta_group::2).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_cluster2(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                   cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 #define launch_pdl(...) launch_pdl_kind(1, __VA_ARGS__)
 #define launch_pdl_conv(...) launch_pdl_kind(2, __VA_ARGS__)
 

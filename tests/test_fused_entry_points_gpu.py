@@ -330,3 +330,37 @@ def test_stride2_dgrad_by_parity_phases(N, H, C, K):
     assert (dm.t.float() - want).abs().max() <= 1e-2 * want.abs().max() + 1e-3
     assert torch.allclose(stats[0], dm.t.float().reshape(-1, C).sum(0), rtol=1e-3, atol=0.05)
     assert torch.allclose(stats[1], (dm.t.float() * y.float()).reshape(-1, C).sum(0), rtol=1e-3, atol=0.05)
+
+
+@pytest.mark.parametrize("N,H,C,K,ks,mode,bn", [(8, 14, 256, 256, 3, 0, 128), (5, 7, 512, 512, 3, 1, 256),
+                                                (3, 14, 1024, 256, 1, 2, 128), (7, 7, 512, 2048, 1, 1, 128)])
+def test_cta_pair_kernel_equals_single_cta_kernel(N, H, C, K, ks, mode, bn, monkeypatch):
+    """tcgen05 cta_group::2 variant (two CTAs of a cluster share one 256-row MMA, each stages half
+    of the weight tile) against the single-CTA kernel: same products in the same order, so outputs
+    are identical; includes an odd number of row tiles (the last pair has an empty partner)."""
+    from distributed_resnet_tensorflow_b200.ops.conv import ConvGeom, conv_fprop
+    lo = (ks - 1) // 2
+    g = ConvGeom(N, H, H, C, K, ks, ks, 1, lo, ks - 1 - lo)
+    gen = torch.Generator(device="cuda").manual_seed(9)
+    x = torch.randn((N, H, H, C), device="cuda", generator=gen).bfloat16()
+    w = (torch.randn((K, ks, ks, C), device="cuda", generator=gen) / (ks * ks * C) ** 0.5).bfloat16()
+    side = torch.randn((N, g.P, g.Q, K), device="cuda", generator=gen).bfloat16() if mode else None
+    ss = (torch.rand((K, 2), device="cuda", generator=gen) - 0.3) if mode == 2 else None
+    outs = []
+    for two in ("0", "2"):
+        monkeypatch.setenv("DRN_TWO_CTA", two)
+        y = Guarded((N, g.P, g.Q, K), torch.bfloat16)
+        st = torch.zeros((2, K), device="cuda")
+        conv_fprop(x, w, g, out=y.t, side=side, stats=st, bn_scale_shift=ss, mode=mode, force_bn=bn)
+        torch.cuda.synchronize()
+        assert y.intact()
+        outs.append((y.t.clone(), st))
+    assert torch.equal(outs[0][0], outs[1][0])
+    assert torch.allclose(outs[0][1], outs[1][1], rtol=1e-4, atol=1e-3)
+    xf = F.pad(x.float().permute(0, 3, 1, 2), (lo, ks - 1 - lo, lo, ks - 1 - lo))
+    ref = F.conv2d(xf, w.float().permute(0, 3, 1, 2)).permute(0, 2, 3, 1)
+    if mode == 1:
+        ref = ref + side.float()
+    elif mode == 2:
+        ref = ref * ((side.float() * ss[:, 0] + ss[:, 1]) > 0)
+    assert (outs[1][0].float() - ref).abs().max() <= 0.02 * ref.abs().max() + 1e-3
