@@ -759,8 +759,8 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
     default: {
       // CTA pairs (DRN_TWO_CTA: 0 never, 1 policy, 2 always where a variant exists).  Measured
       // (bench/check_two.py): halving the weight traffic pays only where the weights dominate the
-      // L2->SM stream - 3x3 over 512 channels at 7x7, 47 -> 41 us; everywhere else the pair's
-      // lock-step costs as much as it saves (or more: 1x1 256->1024 at 14x14, 46 -> 66 us).
+      // L2->SM stream - 3x3 over 512 channels at 7x7, 49 -> 41 us; everywhere else it ties with the
+      // single-CTA kernel (those layers are bound by their epilogue or by HBM).
       const int two_env = env_int("DRN_TWO_CTA", 1);
       const bool two = current_pre() == nullptr && current_view() == nullptr && (bn == 128 || bn == 256) &&
                        two_env >= 1 && (two_env >= 2 || d.R * d.S * d.C >= 4096);
