@@ -198,11 +198,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         const int oq = rem - op * p.Q;
         const int w0 = oq * p.stride_w - p.pad_w;
         const int h0 = op * p.stride_h - p.pad_h;
+        // (tap, channel block, filter row, filter column) advance incrementally: four integer
+        // divisions per k-step would be a visible part of this single thread's loop
+        int tap = 0, cb = 0, r = 0, s = 0;
         for (int it = 0; it < p.k_iters; ++it) {
-          const int tap = it / p.c_blocks;
-          const int cb = it - tap * p.c_blocks;
-          const int r = tap / p.S;
-          const int s = tap - r * p.S;
           mbar_wait_sleep(empty_bar(stage), phase ^ 1, 0x10 + stage, p.spin_ns);
           const uint32_t a_dst = sStages + stage * C_::kStageBytes;
           const uint32_t b_dst = a_dst + C_::kABytes;
@@ -222,6 +221,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
+          }
+          if (++cb == p.c_blocks) {
+            cb = 0;
+            ++tap;
+            if (++s == p.S) {
+              s = 0;
+              ++r;
+            }
           }
         }
       }
@@ -625,6 +632,7 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   const int k_iters_total = d.R * d.S * ((d.C + KC - 1) / KC);
   p.n_res = mode == DRN_EPI_PLAIN ? 0 : env_int("DRN_NRES", k_iters_total <= 2 ? 4 : 2);
   p.n_stages = C_::stages_for(p.n_res);
+  if (int cap = env_int("DRN_STAGES", 0)) p.n_stages = p.n_stages < cap ? p.n_stages : cap;   // experiments
   if (p.n_stages < 2) return fail("conv_igemm: shared memory plan does not fit (KC=%d BN=%d)", KC, BN);
   const int smem_bytes = C_::smem_for(p.n_res, p.n_stages);
   p.want_stats = stats != nullptr;
