@@ -32,7 +32,7 @@ namespace {
 
 constexpr int kBM = 128;            // output pixels per tile (UMMA M)
 constexpr int kEpiBufs = 2;         // double-buffered epilogue chunk buffers
-constexpr int kNumThreads = 384;    // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4-11 epilogue (2 groups)
+constexpr int kNumThreads = 384;    // warp0 TMA (A), warp1 MMA, warp2 TMEM alloc, warp3 TMA (B), warps 4-11 epilogue (2 groups)
 constexpr int kEpiThreads = 128;
 constexpr int kMaxStages = 8;
 
@@ -153,7 +153,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(full_bar(s), 1);
+      mbar_init(full_bar(s), 2);   // the A producer and the B producer
       mbar_init(empty_bar(s), 1);
     }
     for (int b = 0; b < 2; ++b) {
@@ -183,48 +183,61 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
   // everything above (barriers, TMEM, descriptor prefetch) overlapped the previous kernel's tail
   pdl_wait();
 
-  if (warp == 0) {
-    // ======================= TMA producer =======================
+  if (warp == 0 || warp == 3) {
+    // ======================= TMA producers =======================
+    // Two single-thread producers share every stage: warp 0 issues the im2col loads of the A tile,
+    // warp 3 the loads of the weight tile.  One thread doing both (plus its index arithmetic and
+    // two mbarrier operations per stage) was the slowest stage of the whole pipeline.
+    const bool do_a = warp == 0;
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int t = t_begin; t < t_end; ++t) {
         const int n_tile = t / p.m_tiles;
-        const int m_tile = row_tile(t - n_tile * p.m_tiles);
-        const int m0 = m_tile * kBM;
-        const int img = m0 / p.PQ;
-        const int rem = m0 - img * p.PQ;
-        const int op = rem / p.Q;
-        const int oq = rem - op * p.Q;
-        const int w0 = oq * p.stride_w - p.pad_w;
-        const int h0 = op * p.stride_h - p.pad_h;
-        // (tap, channel block, filter row, filter column) advance incrementally: four integer
-        // divisions per k-step would be a visible part of this single thread's loop
-        int tap = 0, cb = 0, r = 0, s = 0;
+        int img = 0, w0 = 0, h0 = 0;
+        if (do_a) {
+          const int m0 = row_tile(t - n_tile * p.m_tiles) * kBM;
+          img = m0 / p.PQ;
+          const int rem = m0 - img * p.PQ;
+          const int op = rem / p.Q;
+          const int oq = rem - op * p.Q;
+          w0 = oq * p.stride_w - p.pad_w;
+          h0 = op * p.stride_h - p.pad_h;
+        }
+        const int b_row = n_tile * BN + (TWO ? (int)cta_rank * C_::kBRows : 0);
+        // (channel block, filter row, filter column, weight column) advance incrementally: integer
+        // divisions per k-step would be a visible part of a single thread's loop
+        int cb = 0, r = 0, s = 0, b_col = 0;
         for (int it = 0; it < p.k_iters; ++it) {
           mbar_wait_sleep(empty_bar(stage), phase ^ 1, 0x10 + stage, p.spin_ns);
           const uint32_t a_dst = sStages + stage * C_::kStageBytes;
-          const uint32_t b_dst = a_dst + C_::kABytes;
-          if (TWO) {
-            // both CTAs load (own A rows, own half of B); all bytes are counted on the leader's barrier
-            if (leader_cta) mbar_arrive_expect_tx(full_bar(stage), 2 * (C_::kABytes + C_::kBBytesRaw));
-            tma_load_im2col_4d_2cta(a_dst, &tmapA, full_bar(stage), cb * KC, w0, h0, img,
-                                    static_cast<uint16_t>(s), static_cast<uint16_t>(r));
-            tma_load_2d_2cta(b_dst, &tmapB, full_bar(stage), tap * p.C + cb * KC,
-                             n_tile * BN + (int)cta_rank * C_::kBRows);
+          if (do_a) {
+            if (TWO) {
+              // both CTAs of a pair load their own rows; the bytes are counted on the leader's barrier
+              if (leader_cta) mbar_arrive_expect_tx(full_bar(stage), 2 * C_::kABytes);
+              tma_load_im2col_4d_2cta(a_dst, &tmapA, full_bar(stage), cb * KC, w0, h0, img,
+                                      static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+            } else {
+              mbar_arrive_expect_tx(full_bar(stage), C_::kABytes);
+              tma_load_im2col_4d(a_dst, &tmapA, full_bar(stage), cb * KC, w0, h0, img,
+                                 static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+            }
           } else {
-            mbar_arrive_expect_tx(full_bar(stage), C_::kABytes + C_::kBBytesRaw);
-            tma_load_im2col_4d(a_dst, &tmapA, full_bar(stage), cb * KC, w0, h0, img,
-                               static_cast<uint16_t>(s), static_cast<uint16_t>(r));
-            tma_load_2d(b_dst, &tmapB, full_bar(stage), tap * p.C + cb * KC, n_tile * BN);
+            if (TWO) {
+              if (leader_cta) mbar_arrive_expect_tx(full_bar(stage), 2 * C_::kBBytesRaw);
+              tma_load_2d_2cta(a_dst + C_::kABytes, &tmapB, full_bar(stage), b_col, b_row);
+            } else {
+              mbar_arrive_expect_tx(full_bar(stage), C_::kBBytesRaw);
+              tma_load_2d(a_dst + C_::kABytes, &tmapB, full_bar(stage), b_col, b_row);
+            }
           }
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
           }
+          b_col += KC;            // weight columns are ordered (tap, channel): tap * C + cb * KC
           if (++cb == p.c_blocks) {
             cb = 0;
-            ++tap;
             if (++s == p.S) {
               s = 0;
               ++r;

@@ -132,6 +132,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
         int stage = 0;
         uint32_t phase = 0;
         const uint32_t tx_bytes = C_::kABytes + nboxes * C_::kBBoxBytes;
+        // first box of this CTA's column window (constant over the pixel loop): no divisions inside
+        const int tap0 = n0 / p.C, c00 = n0 - tap0 * p.C;
+        const int r0 = tap0 / p.S, s0 = tap0 - r0 * p.S;
         for (int ch = chunk_begin; ch < chunk_end; ++ch) {
           const int m0 = ch * kPix;
           const int img = m0 / p.PQ;
@@ -147,18 +150,17 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
           for (int i = 0; i < C_::kABoxes; ++i)
             tma_load_2d(a_dst + i * C_::kABoxBytes, &tmapDY, full_bar(stage),
                         co_tile * 128 + i * CWA, m0);
-          int flat = n0;
-          int tap = flat / p.C;
-          int c0 = flat - tap * p.C;
+          int c0 = c00, r = r0, s = s0;
           for (int i = 0; i < nboxes; ++i) {
-            const int r = tap / p.S;
-            const int s = tap - r * p.S;
             tma_load_im2col_4d(b_dst + i * C_::kBBoxBytes, &tmapX, full_bar(stage), c0, w0, h0, img,
                                static_cast<uint16_t>(s), static_cast<uint16_t>(r));
             c0 += CWB;
             if (c0 >= p.C) {
               c0 = 0;
-              ++tap;
+              if (++s == p.S) {
+                s = 0;
+                ++r;
+              }
             }
           }
           if (++stage == kStages) {
