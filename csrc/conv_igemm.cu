@@ -416,28 +416,35 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
       }
       named_bar_sync(bar_id, kEpiThreads);
     };
-    // (tile, chunk) of the idx-th chunk this group processes
-    auto locate = [&](uint32_t idx, int& tile, int& chunk) {
-      const uint32_t gg = idx * 2 + grp;
-      tile = t_begin + (int)(gg / C_::kChunks);
-      chunk = (int)(gg % C_::kChunks);
-    };
-    auto issue_res_load = [&](uint32_t idx) {
-      int tile, chunk;
-      locate(idx, tile, chunk);
-      if (tile >= t_end) return;
-      const int n_tile = tile / p.m_tiles;
-      const int m_tile = row_tile(tile - n_tile * p.m_tiles);
-      const uint32_t b = idx % n_res;
-      mbar_arrive_expect_tx(res_bar(grp * kMaxRes + b), C_::kChunkBytes);
-      tma_load_2d(res_base + b * C_::kChunkBytes, &tmapR, res_bar(grp * kMaxRes + b),
-                  n_tile * BN + chunk * kCW, m_tile * kBM);
+    // Side-input prefetch cursor (leader thread only): the group's chunks are requested strictly in
+    // order, so (tile, chunk, column tile, row index, ring slot) advance incrementally - the leader
+    // runs this once per chunk while 127 threads wait for it, no runtime divisions here.
+    int pf_tile = t_begin + grp / C_::kChunks, pf_chunk = grp % C_::kChunks;
+    int pf_n = pf_tile / p.m_tiles, pf_m = pf_tile - pf_n * p.m_tiles;
+    uint32_t pf_slot = 0;
+    auto issue_next_res_load = [&]() {
+      if (pf_tile < t_end) {
+        mbar_arrive_expect_tx(res_bar(grp * kMaxRes + pf_slot), C_::kChunkBytes);
+        tma_load_2d(res_base + pf_slot * C_::kChunkBytes, &tmapR, res_bar(grp * kMaxRes + pf_slot),
+                    pf_n * BN + pf_chunk * kCW, row_tile(pf_m) * kBM);
+      }
+      if (++pf_slot == n_res) pf_slot = 0;
+      pf_chunk += 2;                       // the other group takes the chunks in between
+      while (pf_chunk >= C_::kChunks) {
+        pf_chunk -= C_::kChunks;
+        ++pf_tile;
+        if (++pf_m == p.m_tiles) {
+          pf_m = 0;
+          ++pf_n;
+        }
+      }
     };
 
     uint32_t mine = 0;  // chunks processed by this group so far
+    uint32_t rb = 0, rb_phase = 0;  // ring slot / phase of the chunk being processed (= mine % n_res, ...)
     if (has_res && leader) {
       // fill the ring: chunks 0 .. n_res-2 (chunk i + n_res - 1 is requested when chunk i starts)
-      for (uint32_t i = 0; i + 1 < n_res; ++i) issue_res_load(i);
+      for (uint32_t i = 0; i + 1 < n_res; ++i) issue_next_res_load();
     }
 
     int acc = 0;
@@ -467,11 +474,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         for (int a = 0; a < kHalf; ++a) {
           const int j = C_::kChunks >= 2 ? 2 * a + grp : 0;
           const uint32_t out_buf = out_base + (mine & 1) * C_::kChunkBytes;
-          const uint32_t rb = has_res ? mine % n_res : 0;
           const uint32_t res_buf = res_base + rb * C_::kChunkBytes;
           // request the side input n_res-1 chunks ahead; it lands in the ring slot whose last
           // readers finished before the closing barrier of the previous chunk
-          if (has_res && leader) issue_res_load(mine + n_res - 1);
+          if (has_res && leader) issue_next_res_load();
 
           // ---- TMEM -> registers (kCW fp32 columns of my row)
           float v[kCW];
@@ -506,7 +512,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           }
 
           if (has_res) {
-            mbar_wait_sleep(res_bar(grp * kMaxRes + rb), (mine / n_res) & 1, 0x50 + grp * kMaxRes + rb, p.spin_ns);
+            mbar_wait_sleep(res_bar(grp * kMaxRes + rb), rb_phase, 0x50 + grp * kMaxRes + rb, p.spin_ns);
             if (p.mode == DRN_EPI_RESADD) {
 #pragma unroll
               for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
@@ -589,6 +595,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           if (leader) tma_store_wait_read<1>();
           named_bar_sync(bar_id, kEpiThreads);
           ++mine;
+          if (has_res && ++rb == n_res) {
+            rb = 0;
+            rb_phase ^= 1;
+          }
         }
       }
       acc ^= 1;
