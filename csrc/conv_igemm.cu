@@ -302,7 +302,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         const int m_tile = t - n_tile * p.m_tiles;
         const long long m0 = (long long)m_tile * kBM;
         for (int it = 0; it < p.k_iters; ++it) {
-          const int cb = it % p.c_blocks;
+          const int cb = it;   // 1x1 only: the k-step IS the channel block
           const float4* sp = reinterpret_cast<const float4*>(p.pre_ss + cb * KC + g * 8);
           float4 q[4];
 #pragma unroll

@@ -135,12 +135,18 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
         // first box of this CTA's column window (constant over the pixel loop): no divisions inside
         const int tap0 = n0 / p.C, c00 = n0 - tap0 * p.C;
         const int r0 = tap0 / p.S, s0 = tap0 - r0 * p.S;
+        // output-pixel cursor (image, row, column) of the chunk's first pixel, advanced incrementally
+        const int Pn = p.PQ / p.Q;
+        int img, op, oq;
+        {
+          const int m_first = chunk_begin * kPix;
+          img = m_first / p.PQ;
+          const int rem = m_first - img * p.PQ;
+          op = rem / p.Q;
+          oq = rem - op * p.Q;
+        }
         for (int ch = chunk_begin; ch < chunk_end; ++ch) {
           const int m0 = ch * kPix;
-          const int img = m0 / p.PQ;
-          const int rem = m0 - img * p.PQ;
-          const int op = rem / p.Q;
-          const int oq = rem - op * p.Q;
           const int w0 = oq * p.stride - p.pad_w, h0 = op * p.stride - p.pad;
           mbar_wait(empty_bar(stage), phase ^ 1, 0x110 + stage);
           const uint32_t a_dst = sStages + stage * C_::kStageBytes;
@@ -166,6 +172,14 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
+          }
+          oq += kPix;
+          while (oq >= p.Q) {
+            oq -= p.Q;
+            if (++op == Pn) {
+              op = 0;
+              ++img;
+            }
           }
         }
       }
@@ -210,11 +224,12 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
         const int r0 = tt >> 3;  // rows r0 + 16 * j
         int stage = 0;
         uint32_t phase = 0;
+        const int c_first = n0 % p.C;   // input channel of the first box (boxes wrap from tap to tap)
         for (int ch = 0; ch < n_chunks; ++ch) {
           mbar_wait(full_bar(stage), phase, 0x160 + stage);
           const uint32_t b_addr = sStages + stage * C_::kStageBytes + C_::kABytes;
-          for (int i = 0; i < nboxes; ++i) {
-            const int c0 = (n0 + i * CWB) % p.C;
+          int c0 = c_first;
+          for (int i = 0; i < nboxes; ++i, c0 = (c0 + CWB >= p.C) ? 0 : c0 + CWB) {
             const float4* sp = reinterpret_cast<const float4*>(p.pre_ss + c0 + g * 8);
             float4 q[4];
 #pragma unroll
