@@ -688,11 +688,11 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
     DRN_REQUIRE(p.pre_ss == nullptr, "conv_igemm: no CTA-pair variant of the BatchNorm prologue");
     const int pairs = num_sms() / 2;
     grid = 2 * (p.total_tiles < pairs ? p.total_tiles : pairs);
-    static bool attr_set_two = false;
-    if (!attr_set_two) {
+    static PerDeviceOnce attr_set_two;
+    if (attr_set_two.need()) {
       DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN, false, true>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
-      attr_set_two = true;
+      attr_set_two.mark();
     }
     DRN_CHECK_CUDA(launch_cluster2(conv_igemm_kernel<KC, BN, false, true>, dim3(grid), dim3(kNumThreads),
                                    smem_bytes, stream, tA, tB, tC, tR, p));
@@ -702,11 +702,11 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
     if constexpr (KC == 64 && (BN == 64 || BN == 128)) {
       DRN_REQUIRE(d.R == 1 && d.S == 1 && d.pad_lo == 0 && d.pad_hi == 0 && view == nullptr,
                   "conv_igemm: the BatchNorm prologue supports 1x1 convolutions only");
-      static bool attr_set_pre = false;
-      if (!attr_set_pre) {
+      static PerDeviceOnce attr_set_pre;
+      if (attr_set_pre.need()) {
         DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN, true>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
-        attr_set_pre = true;
+        attr_set_pre.mark();
       }
       DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN, true>, dim3(grid),
                                      dim3(kNumThreads + kPreThreads), smem_bytes, stream, tA, tB, tC, tR, p));
@@ -715,11 +715,11 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
       return fail("conv_igemm: the BatchNorm prologue needs C %% 64 == 0 and an N tile of 64 or 128 (got KC=%d BN=%d)", KC, BN);
     }
   }
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_set;
+  if (attr_set.need()) {
     DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
-    attr_set = true;
+    attr_set.mark();
   }
   DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN>, dim3(grid), dim3(kNumThreads), smem_bytes, stream,
                             tA, tB, tC, tR, p));

@@ -352,21 +352,21 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
                                d.pad_hi - (d.R - 1), pad_w_hi - (d.S - 1), d.stride, d.stride, CWB,
                                kPix, C_::kRBB, view ? vstr : nullptr))
     return e;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_set;
+  if (attr_set.need()) {
     DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<CWA, CWB>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         C_::kSmemBytes));
-    attr_set = true;
+    attr_set.mark();
   }
   const int grid = units * splits;
   if (p.pre_ss != nullptr) {
     if constexpr (CWB == 64) {
-      static bool attr_set_pre = false;
-      if (!attr_set_pre) {
+      static PerDeviceOnce attr_set_pre;
+      if (attr_set_pre.need()) {
         DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<CWA, CWB, true>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, C_::kSmemBytes));
-        attr_set_pre = true;
+        attr_set_pre.mark();
       }
       DRN_CHECK_CUDA(launch_pdl_conv(conv_wgrad_kernel<CWA, CWB, true>, dim3(grid), dim3(kThreads + kPreThreads),
                                      C_::kSmemBytes, stream, tDY, tX, p));

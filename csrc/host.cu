@@ -42,6 +42,11 @@ int pdl_mask() {
   return m;
 }
 
+int current_device() {
+  int dev = -1;
+  return cudaGetDevice(&dev) == cudaSuccess ? dev : -1;
+}
+
 int num_sms() {
   static int cached[64] = {0};
   int dev = 0;

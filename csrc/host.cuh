@@ -33,6 +33,21 @@ int fail(const char* fmt, ...);
   } while (0)
 
 int num_sms();
+int current_device();   // -1 on error
+
+// "done once per device" latch for per-function attributes (cudaFuncSetAttribute is per device; the
+// library may be used on several GPUs from one process).
+struct PerDeviceOnce {
+  bool done[64] = {};
+  bool need() {
+    const int d = current_device();
+    return d < 0 || d >= 64 || !done[d];
+  }
+  void mark() {
+    const int d = current_device();
+    if (d >= 0 && d < 64) done[d] = true;
+  }
+};
 
 // Programmatic dependent launch: the kernel may be scheduled while its predecessor in the stream is
 // still draining; it must execute pdl_wait() (common.cuh) before touching memory the predecessor
