@@ -31,7 +31,7 @@ namespace drn {
 namespace {
 
 constexpr int kBM = 128;            // output pixels per tile (UMMA M)
-constexpr int kEpiBufs = 2;         // double-buffered epilogue chunk buffers
+constexpr int kEpiBufs = 3;         // staging buffers per epilogue group (three: ONE barrier per chunk)
 constexpr int kNumThreads = 384;    // warp0 TMA (A), warp1 MMA, warp2 TMEM alloc, warp3 TMA (B), warps 4-11 epilogue (2 groups)
 constexpr int kEpiThreads = 128;
 constexpr int kMaxStages = 8;
@@ -74,7 +74,7 @@ struct Cfg {
   static constexpr int kChunks = BN / kCW;
   static constexpr int kRowBytes = kCW * 2;            // bytes per staged row (= swizzle span)
   static constexpr int kChunkBytes = kBM * kRowBytes;  // <= 8 KB
-  static constexpr int kOutBytes = 2 * kEpiBufs * kChunkBytes;   // 2 groups x out[2]
+  static constexpr int kOutBytes = 2 * kEpiBufs * kChunkBytes;   // 2 groups x out[kEpiBufs]
   static constexpr int kAuxBytes = 4096 + 2048 + 1024;  // 2 x scale/shift cache, 2 x stats scratch, barriers
   static constexpr int kTmemColsRaw = 2 * BN;
   static constexpr int kTmemCols = kTmemColsRaw <= 32    ? 32
@@ -442,6 +442,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 
     uint32_t mine = 0;  // chunks processed by this group so far
     uint32_t rb = 0, rb_phase = 0;  // ring slot / phase of the chunk being processed (= mine % n_res, ...)
+    uint32_t ob = 0;                // staging buffer of the chunk being processed (= mine % kEpiBufs)
+    const bool late_refill = p.want_stats && p.mode == DRN_EPI_BNBWD;
     if (has_res && leader) {
       // fill the ring: chunks 0 .. n_res-2 (chunk i + n_res - 1 is requested when chunk i starts)
       for (uint32_t i = 0; i + 1 < n_res; ++i) issue_next_res_load();
@@ -473,11 +475,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 #pragma unroll
         for (int a = 0; a < kHalf; ++a) {
           const int j = C_::kChunks >= 2 ? 2 * a + grp : 0;
-          const uint32_t out_buf = out_base + (mine & 1) * C_::kChunkBytes;
+          const uint32_t out_buf = out_base + ob * C_::kChunkBytes;
           const uint32_t res_buf = res_base + rb * C_::kChunkBytes;
-          // request the side input n_res-1 chunks ahead; it lands in the ring slot whose last
-          // readers finished before the closing barrier of the previous chunk
-          if (has_res && leader) issue_next_res_load();
+          // request the side input n_res-1 chunks ahead; it lands in the ring slot of the previous
+          // chunk, whose main-pass readers all passed that chunk's barrier.  When the statistics read
+          // the side tile too (BNBWD), they may still be running: refill after THIS chunk's barrier.
+          if (has_res && leader && !late_refill) issue_next_res_load();
 
           // ---- TMEM -> registers (kCW fp32 columns of my row)
           float v[kCW];
@@ -541,7 +544,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
             }
           }
 
-          // ---- registers -> swizzled smem (bf16); out_buf is free (closing barrier, last chunk)
+          // ---- registers -> swizzled smem (bf16); out_buf was released by the previous chunk's barrier
 #pragma unroll
           for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
             st_shared_v4(out_buf + row_off[c16], pack_bf16x2(v[c16 * 8 + 0], v[c16 * 8 + 1]),
@@ -550,10 +553,17 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                          pack_bf16x2(v[c16 * 8 + 6], v[c16 * 8 + 7]));
           }
           fence_proxy_async_smem();
+          // The ONE barrier of the chunk.  Before it the leader makes sure that every store but the
+          // newest has finished reading its staging buffer: that frees the buffer of chunk mine-2,
+          // which is the one chunk mine+1 writes (three buffers in rotation).  Everything a thread
+          // does after this barrier for chunk `mine` (the statistics pass) reads buffers that are not
+          // rewritten before the thread itself has passed the next two barriers.
+          if (leader) tma_store_wait_read<1>();
           named_bar_sync(bar_id, kEpiThreads);
           if (leader) {
             tma_store_2d(&tmapC, out_buf, n_tile * BN + j * kCW, m_tile * kBM);
             tma_store_commit();
+            if (has_res && late_refill) issue_next_res_load();
           }
 
           // ---- per-channel statistics of what was just stored (bf16-rounded values)
@@ -590,11 +600,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
               }
             }
           }
-          // The other out buffer (next chunk's) was last read by the store issued one chunk ago:
-          // wait for everything but the newest store, then let the whole group move on.
-          if (leader) tma_store_wait_read<1>();
-          named_bar_sync(bar_id, kEpiThreads);
           ++mine;
+          if (++ob == kEpiBufs) ob = 0;
           if (has_res && ++rb == n_res) {
             rb = 0;
             rb_phase ^= 1;
@@ -653,7 +660,11 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   // side-input ring: short reductions leave shared memory for a deeper ring (3 chunks of lookahead),
   // long ones need the pipeline stages more (measured, bench/tune_igemm.py)
   const int k_iters_total = d.R * d.S * ((d.C + KC - 1) / KC);
-  p.n_res = mode == DRN_EPI_PLAIN ? 0 : env_int("DRN_NRES", k_iters_total <= 2 ? 4 : 2);
+  int n_res_dflt = k_iters_total <= 2 ? 4 : 2;
+  // the BN-backward epilogue refills a ring slot half a chunk later (after the chunk's barrier) and
+  // streams a wide side tensor: it wants the deeper ring up to longer reductions (measured)
+  if (mode == DRN_EPI_BNBWD && (k_iters_total <= 4 || (k_iters_total <= 8 && d.K >= 4 * d.C))) n_res_dflt = 4;
+  p.n_res = mode == DRN_EPI_PLAIN ? 0 : env_int("DRN_NRES", n_res_dflt);
   p.n_stages = C_::stages_for(p.n_res);
   if (int cap = env_int("DRN_STAGES", 0)) p.n_stages = p.n_stages < cap ? p.n_stages : cap;   // experiments
   if (p.n_stages < 2) return fail("conv_igemm: shared memory plan does not fit (KC=%d BN=%d)", KC, BN);
@@ -773,7 +784,7 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
     if (d.K % 256 == 0) {
       const long long r128 = (m_tiles * (d.K / 128) + sms - 1) / sms;
       const long long r256 = (m_tiles * (d.K / 256) + sms - 1) / sms;
-      const double w256 = (mode != DRN_EPI_PLAIN && k_iters < 32) ? 2.2 : 1.9;  // epilogue-heavy when K is short
+      const double w256 = mode != DRN_EPI_PLAIN ? 2.2 : 1.9;  // side modes: 3 staging buffers + ring leave 256-wide tiles 2 stages
       bn = (k_iters == 1 || r256 * w256 < (double)r128) ? 256 : 128;
       if (current_pre() != nullptr) bn = 128;   // the prologue variant exists for N tiles <= 128
     } else if (d.K % 128 == 0) bn = 128;
