@@ -195,3 +195,49 @@ def make_reducer(mode: str, rank: int, world: int, device, algo: str = "auto",
     if mode in ("ps", "parameter_server"):
         return ParameterServerReducer(rank, world, device, num_ps=num_ps, algo=algo, **kw)
     raise ValueError(f"unknown parallel mode {mode!r}")
+
+
+class LocalBucketedOptimizer:
+    """Single replica: nothing to reduce, but the momentum-SGD update still runs bucket by bucket on
+    a side stream as soon as backward has finished an arena range (the way both data-parallel
+    strategies do), so only the last bucket's update is exposed at the end of the step."""
+
+    def __init__(self, device, bucket_elems: int = 4 << 20):
+        self.device = torch.device(device)
+        self.bucket_elems = bucket_elems
+        self.stream = torch.cuda.Stream(device=self.device)
+        self._ev_pool: List[torch.cuda.Event] = []
+        self._ev_next = 0
+
+    def _event(self) -> torch.cuda.Event:
+        if self._ev_next == len(self._ev_pool):
+            self._ev_pool.append(torch.cuda.Event())
+        ev = self._ev_pool[self._ev_next]
+        self._ev_next += 1
+        return ev
+
+    def backward_and_update(self, engine) -> None:
+        cur = torch.cuda.current_stream()
+        cs = self.stream
+        self._ev_next = 0
+        pending: List[Tuple[int, int]] = []
+
+        def hook(lo: int, hi: int, last: bool):
+            pending.append((lo, hi))
+            lo_all = min(p[0] for p in pending)
+            hi_all = max(p[1] for p in pending)
+            if not (last or hi_all - lo_all >= self.bucket_elems):
+                return
+            pending.clear()
+            ev = self._event()
+            ev.record(cur)
+            cs.wait_event(ev)
+            wg = engine.last_wgrad_event()      # filter gradients of the range (second stream)
+            if wg is not None:
+                cs.wait_event(wg)
+            _nl.call("drn_sgd_momentum", _p(engine.master[lo_all:]), _p(engine.grad[lo_all:]),
+                     _p(engine.mom[lo_all:]), _p(engine.shadow[lo_all:]), hi_all - lo_all, _p(engine.hyper),
+                     _p(engine.scalars[1:]), 1, cs.cuda_stream)
+
+        engine.backward(range_hook=hook)
+        cur.wait_stream(cs)

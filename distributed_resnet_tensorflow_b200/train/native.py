@@ -17,6 +17,8 @@ from __future__ import annotations
 
 from typing import Dict, Optional
 
+import os
+
 import numpy as np
 import torch
 
@@ -42,6 +44,11 @@ class NativeTrainer:
         self.momentum = momentum
         self.seed = seed
         self.comm = comm                    # parallel.GradientReducer or None
+        # single replica: per-bucket optimizer under backward (DRN_LOCAL_BUCKETS=0: one update at the end)
+        self._local_opt = None
+        if comm is None and os.environ.get("DRN_LOCAL_BUCKETS", "1") != "0":
+            from ..parallel.reducers import LocalBucketedOptimizer
+            self._local_opt = LocalBucketedOptimizer(self.device)
         self.world = comm.world_size if comm is not None else 1
         self.rank = comm.rank if comm is not None else 0
         self.use_graph = use_graph
@@ -93,6 +100,8 @@ class NativeTrainer:
         e.loss(with_grad=True)
         if self.comm is not None:
             self.comm.backward_with_reduction(e)
+        elif self._local_opt is not None:
+            self._local_opt.backward_and_update(e)
         else:
             e.backward()
             e.apply_gradients()
