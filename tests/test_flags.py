@@ -68,3 +68,15 @@ def test_config_defaults_and_validation():
         C.from_flags(F.make_flagset().parse(["--job_name=worker", "--task_index=0"])[0])
     with pytest.raises(ValueError):
         C.from_flags(F.make_flagset().parse(["--job_name=chief", "--task_index=0", "--sync_replicas=True"])[0])
+
+
+def test_input_decode_flag_reaches_the_config_and_defaults_to_host_path():
+    from distributed_resnet_tensorflow_b200.train.loop import use_gpu_decode
+    v, _ = F.make_flagset(**F.IMAGENET_MAIN).parse([])
+    assert v.input_decode == "auto"
+    cfg = C.from_flags(v)
+    assert cfg.train.input_decode == "auto"
+    assert use_gpu_decode(cfg, "cuda:0") is False          # auto stays on the host path (measured equal)
+    assert use_gpu_decode(cfg, None) is False
+    v, _ = F.make_flagset(**F.IMAGENET_MAIN).parse(["--input_decode=cpu"])
+    assert use_gpu_decode(C.from_flags(v), "cuda:0") is False
