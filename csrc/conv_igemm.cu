@@ -92,7 +92,10 @@ struct Cfg {
   }
 };
 
-template <int KC, int BN, bool PRE = false, bool TWO = false>
+// EPI >= 0 fixes (epilogue mode, statistics) at compile time as mode * 2 + stats: the epilogue is
+// unrolled over its chunks, and carrying all three modes in every copy made the kernel large enough
+// to stall on instruction fetch (ncu: no_instruction).  EPI = -1 keeps them run-time parameters.
+template <int KC, int BN, bool PRE = false, bool TWO = false, int EPI = -1>
 __global__ void __launch_bounds__(PRE ? kNumThreads + kPreThreads : kNumThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                   const __grid_constant__ CUtensorMap tmapC, const __grid_constant__ CUtensorMap tmapR,
@@ -108,6 +111,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
   // pair instead of once per CTA.  p.m_tiles then counts row-tile PAIRS.
   const uint32_t cta_rank = TWO ? cluster_ctarank() : 0u;
   const bool leader_cta = cta_rank == 0;
+  const int mode = EPI < 0 ? p.mode : (EPI >> 1);
+  const bool want_stats = EPI < 0 ? (p.want_stats != 0) : ((EPI & 1) != 0);
 
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment: required by the 128B swizzle atom (8 rows x 128 B).
@@ -149,7 +154,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     tma_prefetch_desc(&tmapA);
     tma_prefetch_desc(&tmapB);
     tma_prefetch_desc(&tmapC);
-    if (p.mode != DRN_EPI_PLAIN) tma_prefetch_desc(&tmapR);
+    if (mode != DRN_EPI_PLAIN) tma_prefetch_desc(&tmapR);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -353,7 +358,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     const int quad = warp & 3;               // TMEM lane quadrant this warp may read
     const int row = quad * 32 + lane;        // tile row == TMEM lane
     const bool leader = (et == 0);
-    const bool has_res = (p.mode != DRN_EPI_PLAIN);
+    const bool has_res = (mode != DRN_EPI_PLAIN);
     const uint32_t bar_id = 1 + grp;
     const uint32_t out_base = sOut + grp * kEpiBufs * C_::kChunkBytes;
     const uint32_t res_base = sRes + grp * p.n_res * C_::kChunkBytes;
@@ -385,7 +390,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     // Reduce the per-thread partial sums over the group (shuffles, then shared-memory atomics)
     // and add one value per channel to the global statistics.
     auto flush_stats = [&](int n_tile) {
-      if (!p.want_stats || n_tile < 0) return;
+      if (!want_stats || n_tile < 0) return;
       for (int i = et; i < 2 * kHalf * kCW; i += kEpiThreads) my_red[i] = 0.f;
       named_bar_sync(bar_id, kEpiThreads);
 #pragma unroll
@@ -443,7 +448,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     uint32_t mine = 0;  // chunks processed by this group so far
     uint32_t rb = 0, rb_phase = 0;  // ring slot / phase of the chunk being processed (= mine % n_res, ...)
     uint32_t ob = 0;                // staging buffer of the chunk being processed (= mine % kEpiBufs)
-    const bool late_refill = p.want_stats && p.mode == DRN_EPI_BNBWD;
+    const bool late_refill = want_stats && mode == DRN_EPI_BNBWD;
     if (has_res && leader) {
       // fill the ring: chunks 0 .. n_res-2 (chunk i + n_res - 1 is requested when chunk i starts)
       for (uint32_t i = 0; i + 1 < n_res; ++i) issue_next_res_load();
@@ -460,7 +465,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         if (n_tile != cur_n_tile) {
           flush_stats(cur_n_tile);
           cur_n_tile = n_tile;
-          if (p.mode == DRN_EPI_BNBWD) {
+          if (mode == DRN_EPI_BNBWD) {
             named_bar_sync(bar_id, kEpiThreads);
             for (int i = et; i < BN; i += kEpiThreads) {
               const int col = n_tile * BN + i;
@@ -516,7 +521,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 
           if (has_res) {
             mbar_wait_sleep(res_bar(grp * kMaxRes + rb), rb_phase, 0x50 + grp * kMaxRes + rb, p.spin_ns);
-            if (p.mode == DRN_EPI_RESADD) {
+            if (mode == DRN_EPI_RESADD) {
 #pragma unroll
               for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
                 const uint4 rv = ld_shared_v4(res_buf + row_off[c16]);
@@ -567,8 +572,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           }
 
           // ---- per-channel statistics of what was just stored (bf16-rounded values)
-          if (p.want_stats) {
-            if (p.mode == DRN_EPI_BNBWD) {
+          if (want_stats) {
+            if (mode == DRN_EPI_BNBWD) {
 #pragma unroll
               for (int i = 0; i < kNcg; ++i) {
                 const uint4 ov = ld_shared_v4(out_buf + st_off[i]);
@@ -628,6 +633,44 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 inline int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return v ? atoi(v) : dflt;
+}
+
+template <int KC, int BN, bool PRE, bool TWO, int EPI>
+int launch_instance(int grid, int threads, int smem_bytes, cudaStream_t stream, const CUtensorMap& tA,
+                    const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tR, const ConvParams& p) {
+  static PerDeviceOnce attr_set;
+  if (attr_set.need()) {
+    DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN, PRE, TWO, EPI>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
+    attr_set.mark();
+  }
+  if constexpr (TWO) {
+    DRN_CHECK_CUDA(launch_cluster2(conv_igemm_kernel<KC, BN, PRE, TWO, EPI>, dim3(grid), dim3(threads),
+                                   smem_bytes, stream, tA, tB, tC, tR, p));
+  } else {
+    DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN, PRE, TWO, EPI>, dim3(grid), dim3(threads),
+                                   smem_bytes, stream, tA, tB, tC, tR, p));
+  }
+  return 0;
+}
+
+// (mode, statistics) combinations the networks use get their own instantiation for the 64-channel
+// k-block kernels (ImageNet-sized layers); everything else runs the generic one.
+template <int KC, int BN, bool PRE, bool TWO>
+int launch_variant(int epi, int grid, int threads, int smem_bytes, cudaStream_t stream, const CUtensorMap& tA,
+                   const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tR, const ConvParams& p) {
+  if constexpr (KC == 64 && BN >= 64) {
+    switch (epi) {
+      case 0: return launch_instance<KC, BN, PRE, TWO, 0>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
+      case 1: return launch_instance<KC, BN, PRE, TWO, 1>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
+      default: break;
+    }
+    if constexpr (!PRE) {
+      if (epi == 3) return launch_instance<KC, BN, PRE, TWO, 3>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
+      if (epi == 5) return launch_instance<KC, BN, PRE, TWO, 5>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
+    }
+  }
+  return launch_instance<KC, BN, PRE, TWO, -1>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
 }
 
 template <int KC, int BN, bool TWO = false>
@@ -695,46 +738,24 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   p.pre_ss = reinterpret_cast<const float2*>(current_pre());
   p.M = M;
   p.spin_ns = (unsigned)env_int("DRN_SPIN_NS", 0);
+  const int epi = mode * 2 + (stats != nullptr ? 1 : 0);
   if constexpr (TWO) {
     DRN_REQUIRE(p.pre_ss == nullptr, "conv_igemm: no CTA-pair variant of the BatchNorm prologue");
     const int pairs = num_sms() / 2;
     grid = 2 * (p.total_tiles < pairs ? p.total_tiles : pairs);
-    static PerDeviceOnce attr_set_two;
-    if (attr_set_two.need()) {
-      DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN, false, true>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
-      attr_set_two.mark();
-    }
-    DRN_CHECK_CUDA(launch_cluster2(conv_igemm_kernel<KC, BN, false, true>, dim3(grid), dim3(kNumThreads),
-                                   smem_bytes, stream, tA, tB, tC, tR, p));
-    return 0;
+    return launch_variant<KC, BN, false, true>(epi, grid, kNumThreads, smem_bytes, stream, tA, tB, tC, tR, p);
   }
   if (p.pre_ss != nullptr) {
     if constexpr (KC == 64 && (BN == 64 || BN == 128)) {
       DRN_REQUIRE(d.R == 1 && d.S == 1 && d.pad_lo == 0 && d.pad_hi == 0 && view == nullptr,
                   "conv_igemm: the BatchNorm prologue supports 1x1 convolutions only");
-      static PerDeviceOnce attr_set_pre;
-      if (attr_set_pre.need()) {
-        DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN, true>,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
-        attr_set_pre.mark();
-      }
-      DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN, true>, dim3(grid),
-                                     dim3(kNumThreads + kPreThreads), smem_bytes, stream, tA, tB, tC, tR, p));
-      return 0;
+      return launch_variant<KC, BN, true, false>(epi, grid, kNumThreads + kPreThreads, smem_bytes, stream, tA,
+                                                 tB, tC, tR, p);
     } else {
       return fail("conv_igemm: the BatchNorm prologue needs C %% 64 == 0 and an N tile of 64 or 128 (got KC=%d BN=%d)", KC, BN);
     }
   }
-  static PerDeviceOnce attr_set;
-  if (attr_set.need()) {
-    DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
-    attr_set.mark();
-  }
-  DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN>, dim3(grid), dim3(kNumThreads), smem_bytes, stream,
-                            tA, tB, tC, tR, p));
-  return 0;
+  return launch_variant<KC, BN, false, false>(epi, grid, kNumThreads, smem_bytes, stream, tA, tB, tC, tR, p);
 }
 
 template <int KC>
