@@ -138,6 +138,10 @@ def main():
     ap.add_argument("--resnet_size", type=int, default=50)
     ap.add_argument("--mode", default="allreduce", choices=["allreduce", "ps"])
     ap.add_argument("--algo", default="auto")
+    ap.add_argument("--pull", default="push", choices=["push", "pull"],
+                    help="--mode ps: owner pushes the new weights / first consuming conv pulls them")
+    ap.add_argument("--sustain_s", type=float, default=3.0,
+                    help="also report a run of at least this many seconds (0 = skip)")
     ap.add_argument("--no_graph", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -192,7 +196,7 @@ def main():
         comm = None
         if world > 1:
             from distributed_resnet_tensorflow_b200.parallel import make_reducer
-            comm = make_reducer(args.mode, rank, world, device, algo=args.algo)
+            comm = make_reducer(args.mode, rank, world, device, algo=args.algo, pull=args.pull)
         tr = NativeTrainer(spec, B, device=device, weight_decay=wd, momentum=0.9, seed=0,
                            use_graph=not args.no_graph, comm=comm)
         tr.import_variables(variables)
@@ -246,12 +250,31 @@ def main():
     ms_e2e = timed_region(e2e_step, args.steps, sync, barrier)
     if "prev" in last and args.impl == "native":
         last["metrics"] = tr.read_metrics(last["prev"])
+    # a longer run next to the K-step burst: seconds of back-to-back steps, where the power cap settles
+    ms_sus, n_sus, clocks_sus = None, 0, None
+    if args.sustain_s > 0:
+        n_sus = max(int(args.sustain_s * 1e3 / max(ms / args.steps, 1e-3)) + 1, args.steps)
+        sampler2 = ClockSampler(local)
+        if rank == 0:
+            sampler2.start()
+        ms_sus = timed_region(device_step, n_sus, sync, barrier)
+        clocks_sus = sampler2.stop() if rank == 0 else None
 
     if world > 1:
-        t = torch.tensor([ms, ms_e2e], device=device, dtype=torch.float64)
+        t = torch.tensor([ms, ms_e2e, ms_sus or 0.0], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(t[0]), float(t[1])
+        ms_sus = float(t[2]) if ms_sus is not None else None
 
+    comm_info = None
+    if args.impl == "native" and world > 1:
+        if args.mode == "ps":
+            comm_info = {"path": "ps", "num_ps": comm.num_ps, "weights": "pull (fused into the first consuming conv)"
+                         if comm.pull else "push (owner stores into every replica)",
+                         "nvls_multimem": bool(comm.use_multicast())}
+        else:
+            comm_info = {"path": "allreduce", "algo": args.algo, "per_bucket": comm.last_algorithms,
+                         "nvls_multimem": bool(comm.use_multicast())}
     if rank == 0:
         gb = B * world
         if args.model == "imagenet":
@@ -274,10 +297,15 @@ def main():
                        "per_gpu_batch": B, "image": f"{img_hw}x{img_hw}x3",
                        "parallelism": f"dp{world}" + ("" if world == 1 else f"_{args.mode}"),
                        "l2_policy": "per-step working set (>5 GB of activations) far exceeds the 126 MB L2",
-                       "cuda_graph": not args.no_graph, "optimizer": "momentum-SGD+L2 on all variables"},
+                       "cuda_graph": not args.no_graph, "optimizer": "momentum-SGD+L2 on all variables",
+                       "collective": comm_info},
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 2), "unit": unit, "ms_per_step": round(ms_e2e / args.steps, 4),
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "sustained": ({"value": round((gb if args.model == "imagenet" else 1) * n_sus / (ms_sus / 1e3), 2),
+                           "unit": unit, "steps": n_sus, "seconds": round(ms_sus / 1e3, 3),
+                           "ms_per_step": round(ms_sus / n_sus, 4), "clocks": clocks_sus}
+                          if ms_sus is not None else None),
             "gpu_launches": (launches_per_step * args.steps) if launches_per_step else 0,
             "last_metrics": last.get("metrics"),
         }

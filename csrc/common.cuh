@@ -24,6 +24,9 @@ namespace drn {
 // error flag written by the watchdog (read back by drn_watchdog_status())
 // ----------------------------------------------------------------------------------------------
 extern __device__ unsigned int g_watchdog_flag;
+// host-visible mailbox (mapped pinned memory, set up by drn_watchdog_arm()): a trap poisons the CUDA
+// context, after which device memory cannot be read back any more - this word can
+extern __device__ unsigned int* g_watchdog_host;
 
 __device__ __forceinline__ uint64_t globaltimer_ns() {
   uint64_t t;
@@ -82,6 +85,8 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 // Bounded wait: traps (and sets g_watchdog_flag = code) after DRN_WATCHDOG_NS.
 static __device__ __noinline__ void watchdog_fire(uint32_t code) {
   atomicExch(&g_watchdog_flag, code);
+  unsigned int* mailbox = g_watchdog_host;
+  if (mailbox != nullptr) *reinterpret_cast<volatile unsigned int*>(mailbox) = code;
   __threadfence_system();
   __trap();
 }
@@ -158,6 +163,12 @@ __device__ __forceinline__ void tma_store_wait_all() {
 // generic-proxy smem writes -> visible to the async proxy (TMA / UMMA)
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// generic-proxy writes to ANY state space (here: global memory another CTA filled and published with
+// a release) -> ordered before this thread's later async-proxy reads (TMA loads)
+__device__ __forceinline__ void fence_proxy_async_all() {
+  asm volatile("fence.proxy.async;" ::: "memory");
 }
 
 // ----------------------------------------------------------------------------------------------

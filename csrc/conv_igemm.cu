@@ -23,6 +23,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "comm_layout.cuh"
 #include "host.cuh"
 #include "../include/drn_b200.h"
 
@@ -57,6 +58,10 @@ struct ConvParams {
   const float2* pre_ss;  // [C] (scale, shift)
   long long M;           // valid output rows (rows beyond are forced to zero after the transform)
   unsigned spin_ns;      // sleep between polls of the non-critical mbarrier waits (0 = spin)
+  // PULL: the filter bank is first fetched from the parameter-server shards (peer memory over
+  // NVLink) into the local working arena by warp 2 of every CTA, each CTA taking 1/gridDim of it;
+  // the weight producer (warp 3) issues its first TMA load only after all CTAs have delivered
+  PullArgs pull;         // pull.shadows.p[0] == nullptr: weights are already local
 };
 constexpr int kPreThreads = 128;    // warps 12-15 of the PRE variant
 
@@ -195,6 +200,22 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     // two mbarrier operations per stage) was the slowest stage of the whole pipeline.
     const bool do_a = warp == 0;
     if (elect_one()) {
+      if (!do_a && p.pull.shadows.p[0] != nullptr) {
+        // all CTAs have delivered their part of the filter bank (generic-proxy stores, released with
+        // __threadfence + atomicAdd); order them before this thread's TMA (async-proxy) reads
+        const uint64_t t0 = globaltimer_ns();
+        uint32_t it = 0;
+        while (ld_acquire_gpu_u32(p.pull.counters) < gridDim.x) {
+          if (((++it) & 0x3f) == 0 && globaltimer_ns() - t0 > DRN_WATCHDOG_NS) watchdog_fire(0x211);
+        }
+        fence_proxy_async_all();
+        // the last CTA through resets the two words for the next launch of this layer
+        if (atomicAdd(p.pull.counters + 1, 1u) == gridDim.x - 1) {
+          p.pull.counters[1] = 0u;
+          __threadfence();
+          p.pull.counters[0] = 0u;
+        }
+      }
       int stage = 0;
       uint32_t phase = 0;
       for (int t = t_begin; t < t_end; ++t) {
@@ -346,6 +367,26 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           }
         }
       }
+    }
+  } else if (warp == 2) {
+    // ======================= weight pull (parameter-server mode) =======================
+    // The all-gather of the SyncReplicas "variable pull" (reference resnet_cifar_main.py:392-396:
+    // variables live on the ps tasks, every worker reads them each step) happens HERE, inside the
+    // first convolution that consumes the weights: the CTAs split the filter bank between them,
+    // wait for the owning shards' epoch flags, and copy their part from the owners' memory over
+    // NVLink into the local arena (which the data- and filter-gradient kernels re-use later),
+    // while warp 0 already streams activation tiles and the pipeline fills.
+    if (p.pull.shadows.p[0] != nullptr) {
+      if (lane == 0) wait_shards_ready(p.pull.my_pad, p.pull.map, p.pull.off, p.pull.count);
+      __syncwarp();
+      const long long g0 = p.pull.off / 8, gn = p.pull.count / 8;
+      const long long per_cta = (gn + gridDim.x - 1) / gridDim.x;
+      long long gb = g0 + per_cta * blockIdx.x, ge = gb + per_cta;
+      if (ge > g0 + gn) ge = g0 + gn;
+      if (gb < ge) pull_groups(p.pull.shadows, p.pull.local_arena, p.pull.map, gb, ge, p.pull.self, lane, 32);
+      __threadfence();      // my part of the bank is in local memory before I say so
+      __syncwarp();
+      if (lane == 0) atomicAdd(p.pull.counters, 1u);
     }
   } else if (warp >= 4 && warp < 12) {
     // ======================= epilogue: two groups of 4 warps =======================
@@ -736,6 +777,8 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
 
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
   p.pre_ss = reinterpret_cast<const float2*>(current_pre());
+  if (current_pull() != nullptr) p.pull = *static_cast<const PullArgs*>(current_pull());
+  else memset(&p.pull, 0, sizeof(p.pull));
   p.M = M;
   p.spin_ns = (unsigned)env_int("DRN_SPIN_NS", 0);
   const int epi = mode * 2 + (stats != nullptr ? 1 : 0);
@@ -939,4 +982,51 @@ extern "C" int drn_conv_dgrad_s2(const drn_conv_desc* desc, const void* dy, cons
     }
   }
   return 0;
+}
+
+// Superset entry point: optional strided view of x, optional BatchNorm+ReLU prologue, and optionally
+// the parameter-server "variable pull" fused in - the kernel first fetches ITS OWN filter bank from
+// the shard owners' memory over NVLink (see the PULL comment in the kernel) and then runs as usual.
+// This is the all-gather of the SyncReplicas path (reference resnet_cifar_main.py:392-396,
+// resnet_model.py:108-112; call site C1 "pull"), placed in the first consumer of the weights.
+extern "C" int drn_conv_igemm_ex(const drn_conv_desc* desc, const drn_conv_view* view,
+                                 const void* pre_scale_shift, const drn_pull_desc* pull, const void* x,
+                                 const void* w, void* y, const void* side, float* stats, int stats_ld,
+                                 const void* bn_scale_shift, int mode, int force_bn, void* stream) {
+  using namespace drn;
+  PullArgs pa;
+  memset(&pa, 0, sizeof(pa));
+  if (pull != nullptr) {
+    DRN_REQUIRE(pull->nranks >= 1 && pull->nranks <= kMaxRanks, "conv_igemm_ex: nranks out of range");
+    DRN_REQUIRE(pull->off % 8 == 0 && pull->count % 8 == 0 && pull->bucket_lo % 8 == 0 && pull->per % 8 == 0,
+                "conv_igemm_ex: pull ranges must be multiples of 8 elements");
+    DRN_REQUIRE(pull->bucket >= 0 && pull->bucket < kMaxBuckets && pull->num_ps >= 1, "conv_igemm_ex: bad shard map");
+    DRN_REQUIRE(pull->counters != nullptr && pull->my_pad != nullptr && pull->local_arena != nullptr,
+                "conv_igemm_ex: pull needs counters, pad and local arena");
+    DRN_REQUIRE(static_cast<const char*>(w) == static_cast<const char*>(pull->local_arena) + 2 * pull->off,
+                "conv_igemm_ex: w must be the layer's slot of the local arena");
+    for (int i = 0; i < pull->nranks; ++i) pa.shadows.p[i] = const_cast<void*>(pull->shadows[i]);
+    pa.my_pad = pull->my_pad;
+    pa.local_arena = pull->local_arena;
+    pa.counters = pull->counters;
+    pa.map.lo = pull->bucket_lo;
+    pa.map.per = pull->per;
+    pa.map.num_ps = pull->num_ps;
+    pa.map.bucket = pull->bucket;
+    pa.off = pull->off;
+    pa.count = pull->count;
+    pa.self = pull->rank;
+    current_pull() = &pa;
+  }
+  ConvView v;
+  if (view != nullptr) {
+    v = ConvView{view->stride_w, view->stride_h, view->stride_n, view->pad_w_lo, view->pad_w_hi};
+    current_view() = &v;
+  }
+  if (pre_scale_shift != nullptr) current_pre() = pre_scale_shift;
+  const int rc = drn_conv_igemm(desc, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, force_bn, stream);
+  current_pre() = nullptr;
+  current_view() = nullptr;
+  current_pull() = nullptr;
+  return rc;
 }

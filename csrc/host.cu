@@ -8,6 +8,8 @@
 namespace drn {
 
 __device__ unsigned int g_watchdog_flag = 0;
+__device__ unsigned int* g_watchdog_host = nullptr;
+static unsigned int* g_mailbox[64] = {};   // host side of the per-device mailbox
 
 std::string& last_error() {
   static thread_local std::string s;
@@ -30,6 +32,11 @@ const ConvView*& current_view() {
 }
 
 const void*& current_pre() {
+  static thread_local const void* v = nullptr;
+  return v;
+}
+
+const void*& current_pull() {
   static thread_local const void* v = nullptr;
   return v;
 }
@@ -169,9 +176,36 @@ extern "C" {
 
 const char* drn_last_error() { return drn::last_error().c_str(); }
 
+// Gives the in-kernel watchdog a word of mapped pinned HOST memory to write its code to, once per
+// device (allocates 4 bytes of pinned memory; call at start-up).  Without it the code lives in
+// device memory only, which is unreadable once a trap has poisoned the context.
+int drn_watchdog_arm() {
+  const int dev = drn::current_device();
+  if (dev < 0 || dev >= 64) return drn::fail("watchdog_arm: no current device");
+  if (drn::g_mailbox[dev] != nullptr) return 0;
+  unsigned int* host = nullptr;
+  DRN_CHECK_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&host), sizeof(unsigned int), cudaHostAllocMapped));
+  *host = 0;
+  unsigned int* dev_alias = nullptr;
+  DRN_CHECK_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&dev_alias), host, 0));
+  DRN_CHECK_CUDA(cudaMemcpyToSymbol(drn::g_watchdog_host, &dev_alias, sizeof(dev_alias)));
+  drn::g_mailbox[dev] = host;
+  return 0;
+}
+
 // 0 if no in-kernel watchdog has fired on the current device; otherwise the code of the
-// barrier that timed out. Clears the flag.
+// barrier that timed out (mbarrier waits 0x10-0x160, collectives 0x200/0x201). Clears the flag.
+// Works after the trap as well when drn_watchdog_arm() was called (host mailbox).
 int drn_watchdog_status() {
+  const int dev = drn::current_device();
+  if (dev >= 0 && dev < 64 && drn::g_mailbox[dev] != nullptr) {
+    volatile unsigned int* box = drn::g_mailbox[dev];
+    const unsigned int code = *box;
+    if (code) {
+      *box = 0;
+      return (int)code;
+    }
+  }
   unsigned int v = 0, z = 0;
   if (cudaMemcpyFromSymbol(&v, drn::g_watchdog_flag, sizeof(v)) != cudaSuccess) return -1;
   if (v) cudaMemcpyToSymbol(drn::g_watchdog_flag, &z, sizeof(z));

@@ -116,5 +116,8 @@ const ConvView*& current_view();
 // Optional BatchNorm+ReLU prologue of the *_pre entry points: float2[C] (scale, shift) applied to the
 // raw input before it is used as an operand (thread-local, set around the ordinary launchers).
 const void*& current_pre();
+// Optional "fetch the filter bank from the parameter-server shards first" request of
+// drn_conv_igemm_ex (thread-local, set around the ordinary launcher); points at a drn::PullArgs.
+const void*& current_pull();
 
 }  // namespace drn

@@ -23,6 +23,14 @@ class ConvDesc(ctypes.Structure):
                 ("N", "H", "W", "C", "K", "R", "S", "stride", "pad_lo", "pad_hi", "P", "Q")]
 
 
+class PullDesc(ctypes.Structure):
+    """drn_pull_desc (include/drn_b200.h)."""
+    _fields_ = [("shadows", ctypes.c_void_p), ("nranks", ctypes.c_int), ("rank", ctypes.c_int),
+                ("my_pad", ctypes.c_void_p), ("local_arena", ctypes.c_void_p), ("counters", ctypes.c_void_p),
+                ("bucket_lo", ctypes.c_longlong), ("per", ctypes.c_longlong), ("num_ps", ctypes.c_int),
+                ("bucket", ctypes.c_int), ("off", ctypes.c_longlong), ("count", ctypes.c_longlong)]
+
+
 class ConvView(ctypes.Structure):
     _fields_ = [("stride_w", ctypes.c_longlong), ("stride_h", ctypes.c_longlong),
                 ("stride_n", ctypes.c_longlong), ("pad_w_lo", ctypes.c_int), ("pad_w_hi", ctypes.c_int)]
@@ -41,9 +49,11 @@ _ll = ctypes.c_longlong
 _SIGNATURES = {
     "drn_last_error": (ctypes.c_char_p, []),
     "drn_watchdog_status": (_i, []),
+    "drn_watchdog_arm": (_i, []),
     "drn_num_sms": (_i, []),
     "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
+    "drn_conv_igemm_ex": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, ctypes.POINTER(PullDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_igemm_view": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_resize_crop_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "drn_weight_prep_dgrad_s2": (_i, [_vp, _vp, _i, _i, _vp]),
@@ -80,8 +90,12 @@ _SIGNATURES = {
     "drn_tfrecord_index": (_ll, [_vp, ctypes.c_size_t, _vp, _vp, _ll, _i]),
     "drn_comm_pad_bytes": (_i, []),
     "drn_allreduce_f32": (_i, [_vp, _vp, _vp, _i, _i, _ll, _ll, _f, _i, _i, _vp]),
-    "drn_ps_update": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _ll, _ll, _vp, _vp, _i, _i, _vp]),
-    "drn_bcast_f32": (_i, [_vp, _vp, _i, _i, _i, _ll, _i, _i, _vp]),
+    "drn_ps_update": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _ll, _ll, _vp, _i, _i, _i, _i, _i, _vp]),
+    "drn_shard_per": (_ll, [_ll, _i]),
+    "drn_allreduce_sgd_oneshot": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _ll, _ll, _vp, _vp, _i, _i, _vp]),
+    "drn_bcast_f32": (_i, [_vp, _vp, _vp, _i, _i, _i, _ll, _i, _i, _vp]),
+    "drn_ps_sync_vectors": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp]),
+    "drn_comm_pad_offset": (_i, [_i]),
     "drn_comm_barrier": (_i, [_vp, _i, _i, _i, _vp]),
     "drn_ipc_alloc": (_i, [ctypes.c_size_t, ctypes.POINTER(_vp), _vp]),
     "drn_ipc_open": (_i, [_vp, ctypes.POINTER(_vp)]),

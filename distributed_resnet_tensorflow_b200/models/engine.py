@@ -28,7 +28,7 @@ import numpy as np
 import torch
 
 from .._native import lib as _nl
-from .._native.lib import ConvDesc, EPI_BNBWD, EPI_PLAIN, EPI_RESADD
+from .._native.lib import ConvDesc, ConvView, EPI_BNBWD, EPI_PLAIN, EPI_RESADD, PullDesc
 from ..ops.conv import ConvGeom
 from .spec import BlockSpec, BNSpec, ConvSpec, NetSpec
 
@@ -250,6 +250,12 @@ class NativeResNet:
             torch.zeros(n, dtype=torch.bfloat16, device=dev)
         assert self.grad.dtype == torch.float32 and self.shadow.dtype == torch.bfloat16
         self.grad.zero_()
+        # parameter-server mode (parallel/reducers.py): gamma / beta / bias are read from an fp32 image
+        # of the bf16 working arena instead of the master (only the shard owner's master is current);
+        # `pre_forward` refreshes it, `pull_plan` tells each convolution where its filter bank lives
+        self.vec_f32 = storage["vec_f32"][:n] if "vec_f32" in storage else None
+        self.pre_forward = None
+        self.pull_plan = None
         self.hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0], device=dev)   # lr, momentum, wd, grad_scale
         self.scalars = torch.zeros(4, device=dev)       # [0] loss_sum, [1] l2_sum
         self.correct = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -271,7 +277,7 @@ class NativeResNet:
         return arena[e.offset:e.offset + e.numel]
 
     def param_view(self, name):
-        return self._view(self.master, name)
+        return self._view(self.vec_f32 if self.vec_f32 is not None else self.master, name)
 
     def grad_view(self, name):
         return self._view(self.grad, name)
@@ -480,8 +486,18 @@ class NativeResNet:
         for c in self._s2_convs:
             _nl.call("drn_weight_prep_dgrad_s2", _p(c.w), _p(c.wd_s2), c.g.K, c.g.C, st)
 
-    def _conv(self, desc, x, w, y, side=None, stats=None, ss=None, mode=EPI_PLAIN, pre=None):
-        """``pre``: (scale, shift) table of a BatchNorm+ReLU to apply to ``x`` on the fly."""
+    def _pull(self, conv_name: Optional[str]):
+        return self.pull_plan.get(f"{conv_name}/kernel") if (self.pull_plan is not None and conv_name) else None
+
+    def _conv(self, desc, x, w, y, side=None, stats=None, ss=None, mode=EPI_PLAIN, pre=None, pull=None,
+              view=None):
+        """``pre``: (scale, shift) table of a BatchNorm+ReLU to apply to ``x`` on the fly; ``pull``:
+        drn_pull_desc of the layer when its weights are still on the parameter-server shards."""
+        if pull is not None or view is not None:
+            _nl.call("drn_conv_igemm_ex", ctypes.byref(desc), ctypes.byref(view) if view is not None else None,
+                     _p(pre), ctypes.byref(pull) if pull is not None else None, _p(x), _p(w), _p(y), _p(side),
+                     _p(stats), stats.stride(0) if stats is not None else 0, _p(ss), mode, 0, self._st())
+            return
         if pre is not None:
             _nl.call("drn_conv_igemm_pre", ctypes.byref(desc), _p(x), _p(pre), _p(w), _p(y), _p(side), _p(stats),
                      stats.stride(0) if stats is not None else 0, _p(ss), mode, 0, self._st())
@@ -490,12 +506,8 @@ class NativeResNet:
                  stats.stride(0) if stats is not None else 0, _p(ss), mode, 0, self._st())
 
     def _stem_conv(self, stats) -> None:
-        if self.stem_view is None:
-            self._conv(self.stem.desc, self.x0, self.stem.w, self.y_stem, stats=stats)
-            return
-        _nl.call("drn_conv_igemm_view", ctypes.byref(self.stem.desc), ctypes.byref(self.stem_view), _p(self.x0),
-                 _p(self.stem.w), _p(self.y_stem), 0, _p(stats), stats.stride(0) if stats is not None else 0,
-                 0, EPI_PLAIN, 0, self._st())
+        self._conv(self.stem.desc, self.x0, self.stem.w, self.y_stem, stats=stats,
+                   pull=self._pull(self.spec.stem.name), view=self.stem_view)
 
     def _event(self):
         if self._ev_next == len(self._ev_pool):
@@ -579,10 +591,13 @@ class NativeResNet:
         """Consumes self.x0 / self.labels; produces self.logits (and saves what backward needs)."""
         s = self.spec
         st = self._st()
+        if self.pre_forward is not None:
+            self.pre_forward(self)
         if training:
             self._stats_arena.zero_()
             self._ev_next = 0
-            self._on_wgrad_stream(self.prep_dgrad_weights, None)
+            if self.pull_plan is None:
+                self._on_wgrad_stream(self.prep_dgrad_weights, None)
         first_bn = self.blocks[0]["bn0"]
         if s.maxpool:
             self._stem_conv(None)
@@ -605,7 +620,11 @@ class NativeResNet:
         hw = x.shape[1] * x.shape[2]
         self._bn_finalize(fb, x.numel() // fb.C, training)
         _nl.call("drn_bnrelu_avgpool", _p(x), _p(fb.ss), _p(self.pooled), self.B, hw, fb.C, st)
-        self._conv(self.dense_desc, self.pooled, self.dense_w, self.logits)
+        self._conv(self.dense_desc, self.pooled, self.dense_w, self.logits, pull=self._pull("dense"))
+        if training and self.pull_plan is not None:
+            # pull mode: the flipped dgrad banks can only be derived once every layer's first consumer
+            # has fetched its weights, i.e. after the forward pass
+            self._on_wgrad_stream(self.prep_dgrad_weights, None)
 
     def _block_fwd(self, b: dict, x, next_bn: _BN, training: bool):
         bn0 = b["bn0"]
@@ -621,7 +640,7 @@ class NativeResNet:
         shortcut = x
         if "proj" in b:
             pj = b["proj"]
-            self._conv(pj.desc, h, pj.w, b["shortcut"], pre=pre)
+            self._conv(pj.desc, h, pj.w, b["shortcut"], pre=pre, pull=self._pull(pj.spec.name))
             shortcut = b["shortcut"]
         convs = b["convs"]
         for i, c in enumerate(convs):
@@ -629,10 +648,11 @@ class NativeResNet:
             y = b["ys"][i]
             if last:
                 self._conv(c.desc, h, c.w, y, side=shortcut, mode=EPI_RESADD,
-                           stats=next_bn.fstats if training else None)
+                           stats=next_bn.fstats if training else None, pull=self._pull(c.spec.name))
             else:
                 bn = b["bns"][i]
-                self._conv(c.desc, h, c.w, y, stats=bn.fstats if training else None, pre=pre if i == 0 else None)
+                self._conv(c.desc, h, c.w, y, stats=bn.fstats if training else None, pre=pre if i == 0 else None,
+                           pull=self._pull(c.spec.name))
                 self._bn_fwd(bn, y, b["acts"][i], training)
                 h = b["acts"][i]
         return b["ys"][-1]

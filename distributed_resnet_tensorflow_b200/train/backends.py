@@ -217,21 +217,30 @@ class TorchBackend:
 class NativeBackend:
     def __init__(self, spec: NetSpec, batch: int, ctx: DistContext, device: str = "cuda:0",
                  weight_decay: float = 1e-4, momentum: float = 0.9, seed: int = 0, cifar_pad: int = 4,
-                 use_graph: bool = True, algo: str = "auto"):
+                 use_graph: bool = True, algo: str = "auto", ps_pull: str = "push"):
         from ..train.native import NativeTrainer
         self.spec, self.B, self.ctx = spec, batch, ctx
         comm = None
         if ctx.distributed:
             from ..parallel import make_reducer
             comm = make_reducer("ps" if ctx.mode == "ps" else "allreduce", ctx.rank, ctx.world, device,
-                                algo=algo, num_ps=ctx.num_ps or None)
+                                algo=algo, num_ps=ctx.num_ps or None, pull=ps_pull)
         self.comm = comm
         self.trainer = NativeTrainer(spec, batch, device=device, weight_decay=weight_decay,
                                      momentum=momentum, seed=seed, use_graph=use_graph, comm=comm,
                                      cifar_pad=cifar_pad)
-        self._pin_i = torch.empty((batch, self.trainer.img_bytes), dtype=torch.uint8).pin_memory()
-        self._pin_l = torch.empty(batch, dtype=torch.int32).pin_memory()
-        self._pin_c = torch.zeros((batch, 3), dtype=torch.int32).pin_memory()
+        # pinned staging ring: slot s is refilled (possibly by the input thread) only after the H2D
+        # copy that read it has completed; `_free` carries (slot, event of that copy)
+        self.PIN_SLOTS = 3
+        self._pin_i = [torch.empty((batch, self.trainer.img_bytes), dtype=torch.uint8).pin_memory()
+                       for _ in range(self.PIN_SLOTS)]
+        self._pin_l = [torch.empty(batch, dtype=torch.int32).pin_memory() for _ in range(self.PIN_SLOTS)]
+        self._pin_c = [torch.zeros((batch, 3), dtype=torch.int32).pin_memory() for _ in range(self.PIN_SLOTS)]
+        self._pin_ev = [torch.cuda.Event() for _ in range(self.PIN_SLOTS)]
+        import queue
+        self._free: "queue.Queue" = queue.Queue()
+        for s_ in range(self.PIN_SLOTS):
+            self._free.put((s_, None))
 
     def import_variables(self, variables):
         self.trainer.import_variables(variables)
@@ -246,26 +255,53 @@ class NativeBackend:
     def global_step(self) -> int:
         return self.trainer.global_step
 
-    def _stage(self, images_u8, labels, crop):
-        if isinstance(images_u8, torch.Tensor) and images_u8.is_cuda:
-            # batch produced on the device (GPU JPEG decode): no pinned bounce for the pixels
-            self._pin_l.copy_(torch.from_numpy(np.asarray(labels, np.int32)))
-            if crop is not None:
-                self._pin_c.copy_(torch.from_numpy(np.asarray(crop, np.int32)))
-            return images_u8.view(self.B, -1), self._pin_l, (self._pin_c if self.spec.dataset == "imagenet" else None)
-        self._pin_i.copy_(torch.from_numpy(np.ascontiguousarray(images_u8).reshape(self.B, -1)))
-        self._pin_l.copy_(torch.from_numpy(np.asarray(labels, np.int32)))
+    # ---- pipelined interface (train/loop.py): prepare on the input thread, submit without a host
+    # sync, fetch metrics only when somebody looks at them -------------------------------------------
+    def prepare_batch(self, images_u8, labels, crop=None):
+        """Copy one host batch into a free pinned slot (thread-safe; blocks while all slots are in
+        flight). Returns an opaque handle for submit_step()."""
+        slot, ev = self._free.get()
+        if ev is not None:
+            try:
+                ev.synchronize()
+            except RuntimeError as e:
+                from .native import raise_if_watchdog
+                raise_if_watchdog(e)
+        on_device = isinstance(images_u8, torch.Tensor) and images_u8.is_cuda
+        if not on_device:   # (GPU JPEG decode delivers device pixels: no pinned bounce for them)
+            self._pin_i[slot].copy_(torch.from_numpy(np.ascontiguousarray(images_u8).reshape(self.B, -1)))
+        self._pin_l[slot].copy_(torch.from_numpy(np.asarray(labels, np.int32)))
         if crop is not None:
-            self._pin_c.copy_(torch.from_numpy(np.asarray(crop, np.int32)))
-        return self._pin_i, self._pin_l, (self._pin_c if self.spec.dataset == "imagenet" else None)
+            self._pin_c[slot].copy_(torch.from_numpy(np.asarray(crop, np.int32)))
+        return slot, (images_u8.view(self.B, -1) if on_device else None)
+
+    def _stage_prepared(self, staged) -> int:
+        slot, dev_pixels = staged
+        pix = dev_pixels if dev_pixels is not None else self._pin_i[slot]
+        c = self._pin_c[slot] if self.spec.dataset == "imagenet" else None
+        dslot = self.trainer.stage_batch(pix, self._pin_l[slot], c)
+        self._pin_ev[slot].record(self.trainer.copy_stream)
+        self._free.put((slot, self._pin_ev[slot]))
+        return dslot
+
+    def submit_step(self, staged, lr: float) -> int:
+        """Enqueue one training step; returns the handle fetch_metrics() takes. No host sync."""
+        return self.trainer.run_staged(self._stage_prepared(staged), lr)
+
+    def fetch_metrics(self, handle: int):
+        """Metrics of a submitted step (waits for it). Valid until two more steps were submitted."""
+        return self.trainer.read_metrics(handle)
 
     def train_step(self, images_u8, labels, lr, crop=None):
-        i, l, c = self._stage(images_u8, labels, crop)
-        return self.trainer.train_step(i, l, lr, c)
+        return self.fetch_metrics(self.submit_step(self.prepare_batch(images_u8, labels, crop), lr))
 
     def profile_step(self) -> str:
         return self.trainer.profile_step()
 
     def eval_batch(self, images_u8, labels, crop=None):
-        i, l, c = self._stage(images_u8, labels, crop)
-        return self.trainer.eval_batch(i, l, c)
+        slot, dev_pixels = self.prepare_batch(images_u8, labels, crop)
+        pix = dev_pixels if dev_pixels is not None else self._pin_i[slot]
+        c = self._pin_c[slot] if self.spec.dataset == "imagenet" else None
+        out = self.trainer.eval_batch(pix, self._pin_l[slot], c)    # synchronises the device
+        self._free.put((slot, None))
+        return out

@@ -15,6 +15,8 @@ from __future__ import annotations
 
 import logging
 import os
+import queue
+import threading
 import time
 from typing import Dict, Iterator, Optional, Tuple
 
@@ -78,6 +80,10 @@ def init_process_group(cfg: Config, ctx: DistContext, device_type: str) -> None:
             os.environ.setdefault("MASTER_PORT", "29500")
             init = "env://"
     dist.init_process_group(backend, init_method=init, rank=ctx.rank, world_size=ctx.world)
+    # collectives among the workers only (checkpoint agreement): with CPU parameter-server tasks in
+    # the process group the ps ranks sit in their serve loop and must not be part of them
+    ctx.worker_group = (dist.new_group(ranks=list(range(ctx.num_workers)))
+                        if ctx.num_workers < ctx.world else None)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -164,7 +170,7 @@ def build_backend(cfg: Config, spec: NetSpec, ctx: DistContext, backend: str, de
     if backend == "native":
         return NativeBackend(spec, batch, ctx, device=device, weight_decay=t.weight_decay,
                              momentum=t.momentum if t.optimizer == "mom" else 0.0, seed=t.seed,
-                             cifar_pad=pad, use_graph=t.cuda_graph, algo=t.allreduce_algo)
+                             cifar_pad=pad, use_graph=t.cuda_graph, algo=t.allreduce_algo, ps_pull=t.ps_pull)
     dtype = "fp32" if device == "cpu" else t.dtype
     return TorchBackend(spec, batch, ctx, device=device, dtype=dtype, weight_decay=t.weight_decay,
                         momentum=t.momentum if t.optimizer == "mom" else 0.0, seed=t.seed, cifar_pad=pad)
@@ -246,54 +252,69 @@ def train(cfg: Config) -> Dict[str, float]:
     saver = Saver(cfg.paths.log_root, t.keep_checkpoint_max) if (cfg.paths.log_root and ctx.is_chief) else None
     summary_dir = cfg.paths.train_dir if cfg.model.dataset == "imagenet" else (cfg.paths.eval_dir or cfg.paths.train_dir)
     writer = EventFileWriter(summary_dir) if (ctx.is_chief and summary_dir) else None
-    batches = training_batches(cfg, spec, ctx, device if backend_name == "native" else None)
+    pipe = _StepPipe(be)
+    feed = _Prefetcher(training_batches(cfg, spec, ctx, device if backend_name == "native" else None),
+                       t.batch_size, pipe.prepare)
     start_step = be.global_step
     t_log, s_log = time.time(), start_step
     metrics: Dict[str, float] = {}
+    handle = None
     local_steps = 0
-    while be.global_step < t.train_steps:
-        if t.max_steps_per_run and local_steps >= t.max_steps_per_run:
-            break
-        lr = sched.before_step()
-        try:
-            imgs, labs, crop = next(batches)
-        except StopIteration:
-            log.info("input exhausted")
-            break
-        if len(labs) != t.batch_size:
-            continue
-        metrics = be.train_step(imgs, labs, lr, crop)
-        local_steps += 1
-        if t.profile and local_steps == 3 and ctx.is_chief and not ctx.distributed and hasattr(be, "profile_step"):
-            log.info("per-kernel device time of one training step:\n%s", be.profile_step())
-        step = be.global_step
-        sched.after_step(step)
-        if step % t.log_every == 0:
-            now = time.time()
-            sps = (step - s_log) / max(now - t_log, 1e-9)
-            t_log, s_log = now, step
-            log.info("step = %d, loss = %.5f, precision = %.4f, lr = %.5f (%.2f global_step/sec, %.1f images/sec)",
-                     step, metrics["cost"], metrics["precision"], lr, sps,
-                     sps * t.batch_size * max(ctx.num_workers, 1))
-            if writer is not None:
-                writer.add_scalars({"global_step/sec": sps}, step)
-        if writer is not None and step % t.summary_every == 0:
-            writer.add_scalars({"cross_entropy": metrics["cross_entropy"], "cost": metrics["cost"],
-                                "learning_rate": lr, "Precision": metrics["precision"]}, step)
-            writer.flush()
-        due = False
-        if saver is not None or (ctx.distributed and ctx.mode == "ps"):
-            if t.save_checkpoint_steps:
-                due = step % t.save_checkpoint_steps == 0
-            elif ctx.is_chief and saver is not None:
-                due = time.time() - saver.last_save_time >= t.save_checkpoint_secs > 0
-            if ctx.distributed and ctx.mode == "ps" and not t.save_checkpoint_steps:
-                due = False  # sharded state needs a collective: only step-based or final saves
-        if due:
-            _save(be, saver, ctx)
+    sharded = ctx.distributed and ctx.mode == "ps"     # saving is a collective over the workers
+    try:
+        while be.global_step < t.train_steps:
+            if t.max_steps_per_run and local_steps >= t.max_steps_per_run:
+                break
+            lr = sched.before_step()
+            staged = feed.next()
+            if staged is None:
+                log.info("input exhausted")
+                break
+            # the step is only ENQUEUED here (native backend): the host keeps running ahead, staging
+            # the next batch while the device works, and looks at the metrics only when a hook needs them
+            handle = pipe.submit(staged, lr)
+            local_steps += 1
+            if t.profile and local_steps == 3 and ctx.is_chief and not ctx.distributed and hasattr(be, "profile_step"):
+                log.info("per-kernel device time of one training step:\n%s", be.profile_step())
+            step = be.global_step
+            sched.after_step(step)
+            want_log = step % t.log_every == 0
+            want_summary = writer is not None and step % t.summary_every == 0
+            if want_log or want_summary:
+                metrics = pipe.metrics(handle)
+            if want_log:
+                now = time.time()
+                sps = (step - s_log) / max(now - t_log, 1e-9)
+                t_log, s_log = now, step
+                log.info("step = %d, loss = %.5f, precision = %.4f, lr = %.5f (%.2f global_step/sec, %.1f images/sec)",
+                         step, metrics["cost"], metrics["precision"], lr, sps,
+                         sps * t.batch_size * max(ctx.num_workers, 1))
+                if writer is not None:
+                    writer.add_scalars({"global_step/sec": sps}, step)
+            if want_summary:
+                writer.add_scalars({"cross_entropy": metrics["cross_entropy"], "cost": metrics["cost"],
+                                    "learning_rate": lr, "Precision": metrics["precision"]}, step)
+                writer.flush()
+            if _checkpoint_due(t, ctx, saver, step, sharded, device):
+                _save(be, saver, ctx)
+        if handle is not None:
+            metrics = pipe.metrics(handle)
+    except Exception as e:
+        from .native import CollectiveTimeout
+        if isinstance(e, CollectiveTimeout):
+            # the context is gone and the peers are in the same state: no checkpoint can be written;
+            # leave with a distinct code so that the launcher restarts the job from the last one
+            log.error("%s - exiting with code %d, resume from the latest checkpoint in %s", e,
+                      EXIT_COLLECTIVE_TIMEOUT, cfg.paths.log_root or "(none)")
+            feed.close()
+            logging.shutdown()
+            os._exit(EXIT_COLLECTIVE_TIMEOUT)
+        raise
+    finally:
+        feed.close()
     # final checkpoint (MonitoredTrainingSession saves on exit)
     if cfg.paths.log_root and not (saver is not None and saver.last_save_step == be.global_step
-                                   and not (ctx.distributed and ctx.mode == "ps")):
+                                   and not sharded):
         _save(be, saver, ctx)
     if ctx.distributed and ctx.mode == "ps" and isinstance(be, TorchBackend):
         be.ps_signal_stop()
@@ -303,6 +324,102 @@ def train(cfg: Config) -> Dict[str, float]:
         open(os.path.join(cfg.paths.log_root, "train.done"), "w").write(str(be.global_step))
     metrics["global_step"] = be.global_step
     return metrics
+
+
+EXIT_COLLECTIVE_TIMEOUT = 86
+
+
+def _checkpoint_due(t, ctx: DistContext, saver: Optional[Saver], step: int, sharded: bool, device: str) -> bool:
+    """CheckpointSaverHook: every --save_checkpoint_steps steps, else every --save_checkpoint_secs
+    seconds (60 s CIFAR / 600 s ImageNet, resnet_cifar_main.py:313,329).  With sharded optimizer
+    state (parameter-server mode) saving is a collective, so the chief's clock decides for everybody:
+    at every logging step it broadcasts one flag to the other workers."""
+    if t.save_checkpoint_steps:
+        return (saver is not None or sharded) and step % t.save_checkpoint_steps == 0
+    if t.save_checkpoint_secs <= 0:
+        return False
+    mine = saver is not None and time.time() - saver.last_save_time >= t.save_checkpoint_secs
+    if not sharded:
+        return mine
+    if step % t.log_every != 0:
+        return False
+    import torch
+    import torch.distributed as dist
+    flag = torch.tensor([1 if mine else 0], dtype=torch.int32,
+                        device=device if device.startswith("cuda") else "cpu")
+    dist.broadcast(flag, src=0, group=getattr(ctx, "worker_group", None))
+    return bool(int(flag.item()))
+
+
+class _StepPipe:
+    """One interface over both backends: the native one enqueues steps and hands out metrics on
+    request (prepare_batch / submit_step / fetch_metrics), the PyTorch one runs a step synchronously."""
+
+    def __init__(self, be):
+        self.be = be
+        self.pipelined = hasattr(be, "submit_step")
+
+    def prepare(self, batch):
+        return self.be.prepare_batch(*batch) if self.pipelined else batch
+
+    def submit(self, staged, lr: float):
+        if self.pipelined:
+            return self.be.submit_step(staged, lr)
+        imgs, labs, crop = staged
+        return self.be.train_step(imgs, labs, lr, crop)
+
+    def metrics(self, handle):
+        return self.be.fetch_metrics(handle) if self.pipelined else handle
+
+
+class _Prefetcher:
+    """Input thread: pulls batches from the reader, drops short ones, copies them into the backend's
+    pinned staging ring (``prepare``) and keeps two of them queued, so that batch assembly overlaps
+    the device step (tf.data's prefetch in the reference, resnet_cifar_main.py:228-236)."""
+
+    def __init__(self, batches: Iterator[Tuple], batch_size: int, prepare, depth: int = 2):
+        self._q: "queue.Queue" = queue.Queue(maxsize=depth)
+        self._stop = threading.Event()
+        self._thread = threading.Thread(target=self._run, args=(batches, batch_size, prepare), daemon=True,
+                                        name="drn-input")
+        self._thread.start()
+
+    def _run(self, batches, batch_size, prepare) -> None:
+        try:
+            for imgs, labs, crop in batches:
+                if self._stop.is_set():
+                    return
+                if len(labs) != batch_size:
+                    continue
+                item = ("ok", prepare((imgs, labs, crop)))
+                while not self._stop.is_set():
+                    try:
+                        self._q.put(item, timeout=0.2)
+                        break
+                    except queue.Full:
+                        pass
+            self._put_final(("end", None))
+        except BaseException as e:          # surfaced on the training thread
+            self._put_final(("error", e))
+
+    def _put_final(self, item) -> None:
+        while not self._stop.is_set():
+            try:
+                self._q.put(item, timeout=0.2)
+                return
+            except queue.Full:
+                pass
+
+    def next(self):
+        kind, val = self._q.get()
+        if kind == "ok":
+            return val
+        if kind == "error":
+            raise val
+        return None
+
+    def close(self) -> None:
+        self._stop.set()
 
 
 def _save(be, saver: Optional[Saver], ctx: DistContext) -> None:

@@ -27,6 +27,28 @@ from ..models.engine import VGG_MEANS, NativeResNet, _p
 from ..models.spec import NetSpec
 
 
+class CollectiveTimeout(RuntimeError):
+    """An in-kernel barrier wait hit the watchdog (a peer replica died or stalled): the CUDA context
+    of this process is gone, the caller should exit and let the launcher resume from the last
+    checkpoint (what MonitoredTrainingSession's session re-creation does for the reference,
+    resnet_cifar_main.py:311-335)."""
+
+    def __init__(self, code: int, cause: str = ""):
+        super().__init__(f"in-kernel barrier wait 0x{code:x} timed out (peer replica dead or stalled?) {cause}")
+        self.code = code
+
+
+def raise_if_watchdog(exc: BaseException) -> None:
+    """Turn a CUDA error that followed a watchdog trap into CollectiveTimeout; otherwise re-raise."""
+    try:
+        code = int(_nl.load().drn_watchdog_status())
+    except Exception:
+        code = 0
+    if code > 0:
+        raise CollectiveTimeout(code, str(exc)[:200]) from exc
+    raise exc
+
+
 class NativeTrainer:
     def __init__(self, spec: NetSpec, batch: int, device: str = "cuda:0", weight_decay: float = 1e-4,
                  momentum: float = 0.9, seed: int = 0, use_graph: bool = True, comm=None,
@@ -40,6 +62,8 @@ class NativeTrainer:
             from ..models.engine import ParamLayout
             storage = comm.allocate(ParamLayout(spec).total)
         self.engine = NativeResNet(spec, batch, device=device, storage=storage)
+        if comm is not None and hasattr(comm, "attach"):
+            comm.attach(self.engine)
         self.weight_decay = weight_decay
         self.momentum = momentum
         self.seed = seed
@@ -75,7 +99,13 @@ class NativeTrainer:
         self._host_metrics = torch.zeros((2, 4), dtype=torch.float32).pin_memory()
         self._host_correct = torch.zeros((2, 1), dtype=torch.int32).pin_memory()
         self._metrics_done = [torch.cuda.Event() for _ in range(2)]
-        self._host_hyper = torch.zeros(4, dtype=torch.float32).pin_memory()
+        # hyper-parameters travel through a small ring of pinned rows: a row is rewritten only after
+        # the H2D copy that read it has completed (the step loop runs ahead of the device, and the
+        # ImageNet warm-up changes the rate every step)
+        self._host_hyper = torch.zeros((8, 4), dtype=torch.float32).pin_memory()
+        self._hyper_done = [None] * 8
+        self._hyper_next = 0
+        _nl.check(_nl.load().drn_watchdog_arm(), "drn_watchdog_arm")
         self.steps_done = 0
         self.h2d_bytes_per_step = batch * img_bytes + batch * 4 + batch * 12
         self.d2h_bytes_per_step = 4 * 4 + 4
@@ -96,10 +126,22 @@ class NativeTrainer:
         e = self.engine
         e.scalars.zero_()
         e.correct.zero_()
+        # parameter-server mode: every owner adds its share of sum(w^2) into every replica's pad
+        l2_slot = getattr(self.comm, "l2_slot", None)
+        pull = l2_slot is not None and self.comm.pull
+        if l2_slot is not None and not pull:
+            l2_slot.zero_()
         e.forward(training=True)
+        if pull:
+            # no closing barrier in pull mode: the owners' contributions of the previous update are
+            # complete once their epoch flags were seen, which forward() has just waited for
+            e.scalars[1:2].copy_(l2_slot)
+            l2_slot.zero_()
         e.loss(with_grad=True)
         if self.comm is not None:
             self.comm.backward_with_reduction(e)
+            if l2_slot is not None and not pull:
+                e.scalars[1:2].copy_(l2_slot)
         elif self._local_opt is not None:
             self._local_opt.backward_and_update(e)
         else:
@@ -111,8 +153,16 @@ class NativeTrainer:
             return
         self._lr = lr
         gs = 1.0 / self.world if (self.comm is not None and self.comm.scale_in_optimizer) else 1.0
-        self._host_hyper.copy_(torch.tensor([lr, self.momentum, self.weight_decay, gs]))
-        self.engine.hyper.copy_(self._host_hyper, non_blocking=True)
+        i = self._hyper_next
+        self._hyper_next = (i + 1) % len(self._hyper_done)
+        if self._hyper_done[i] is not None:
+            self._hyper_done[i].synchronize()
+        row = self._host_hyper[i]
+        row[0], row[1], row[2], row[3] = lr, self.momentum, self.weight_decay, gs
+        self.engine.hyper.copy_(row, non_blocking=True)
+        if self._hyper_done[i] is None:
+            self._hyper_done[i] = torch.cuda.Event()
+        self._hyper_done[i].record(torch.cuda.current_stream())
 
     def _augment(self, slot: int, training: bool, step: int) -> None:
         e = self.engine
@@ -164,7 +214,10 @@ class NativeTrainer:
         return m
 
     def read_metrics(self, m: int) -> Dict[str, float]:
-        self._metrics_done[m].synchronize()
+        try:
+            self._metrics_done[m].synchronize()
+        except RuntimeError as e:       # a trapped kernel surfaces here: name the barrier if it was ours
+            raise_if_watchdog(e)
         loss_sum, l2 = float(self._host_metrics[m, 0]), float(self._host_metrics[m, 1])
         xent = loss_sum / self.B
         return {"cross_entropy": xent, "cost": xent + self.weight_decay * 0.5 * l2,

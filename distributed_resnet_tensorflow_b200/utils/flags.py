@@ -258,7 +258,12 @@ EXTENSION_FLAGS: List[FlagDef] = [
        "gpu (nvJPEG batch decode + one resize/crop kernel, frees the CPU threads), auto = cpu."),
     _b("profile", False, "Print the parameter / FLOP table (tfprof-style) and per-kernel timings."),
     _b("cuda_graph", True, "Capture the training step in a CUDA graph (native backend)."),
-    _s("allreduce_algo", "auto", "auto | oneshot | twoshot | nccl."),
+    _s("allreduce_algo", "auto", "Gradient allreduce of the Horovod path: auto (one-shot for buckets <= 4 MB "
+       "when NVLS multicast is available, else two-shot) | oneshot | twoshot | nccl (library baseline) | "
+       "none; suffix _p2p (or plain p2p) forces peer loads/stores instead of multimem instructions."),
+    _s("ps_pull", "push", "Parameter-server path, how workers get the new weights: push (the shard owner "
+       "stores them into every replica) | pull (the first convolution that consumes a layer fetches it from "
+       "the owners over NVLink)."),
     _n("max_steps_per_run", 0, "Stop this process after N local steps (testing resume)."),
     _s("init_method", "", "torch.distributed init method; default env:// or file-based for "
        "--job_name launches."),

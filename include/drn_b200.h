@@ -24,6 +24,10 @@ extern "C" {
 const char* drn_last_error(void);
 /* Non-zero if a bounded in-kernel barrier wait timed out since the last call (the kernel trapped). */
 int drn_watchdog_status(void);
+/* Give the watchdog a mapped pinned host word to report through (allocates 4 bytes of pinned host
+ * memory once per device): lets drn_watchdog_status() name the stuck barrier even after the trap has
+ * made the CUDA context unusable. (the reference relies on session re-creation.) */
+int drn_watchdog_arm(void);
 int drn_num_sms(void);
 
 /* ---------------------------------------------------------------------------------------------
@@ -76,6 +80,29 @@ int drn_conv_igemm_view(const drn_conv_desc* desc, const drn_conv_view* view, co
 int drn_conv_igemm_pre(const drn_conv_desc* desc, const void* x, const void* pre_scale_shift,
                        const void* w, void* y, const void* side, float* stats, int stats_ld,
                        const void* bn_scale_shift, int mode, int force_bn, void* stream);
+
+/* Parameter-server mode: "this layer's filter bank still lives on the shard owners".  Given to
+ * drn_conv_igemm_ex, the convolution kernel itself performs the pull (all-gather) before it uses the
+ * weights: its CTAs wait for the owners' per-bucket epoch flags (drn_ps_update with pull = 1), copy the
+ * bank from the owners' arenas over NVLink into the local arena and only then start their weight loads;
+ * activation tiles stream in meanwhile.  (Reference: the ps->worker variable read of
+ * replica_device_setter, resnet_cifar_main.py:392-396.) */
+typedef struct {
+  const void* const* shadows; /* HOST array of nranks device pointers: every rank's bf16 working arena */
+  int nranks, rank;
+  const void* my_pad;         /* this rank's signal pad                                           */
+  void* local_arena;          /* this rank's working arena                                        */
+  unsigned int* counters;     /* two zero-initialised device words reserved for this layer        */
+  long long bucket_lo, per;   /* the bucket's first element / elements per owner (drn_shard_per)  */
+  int num_ps, bucket;
+  long long off, count;       /* the layer's weights inside the arena (elements, multiples of 8)  */
+} drn_pull_desc;
+/* drn_conv_igemm with any of: a strided view (NULL = dense), a BatchNorm+ReLU prologue (NULL = none),
+ * a fused weight pull (NULL = weights are local). */
+int drn_conv_igemm_ex(const drn_conv_desc* desc, const drn_conv_view* view, const void* pre_scale_shift,
+                      const drn_pull_desc* pull, const void* x, const void* w, void* y, const void* side,
+                      float* stats, int stats_ld, const void* bn_scale_shift, int mode, int force_bn,
+                      void* stream);
 
 /* Data gradient (K2) of the convolution described by `desc` (FORWARD geometry):
  *   dx[N,H,W,C] = sum_{k,r,s} dy[N,P,Q,K] (x) w,  given w_dgrad = drn_weight_prep_dgrad(w).
@@ -241,14 +268,41 @@ int drn_allreduce_f32(const void* const* bufs, void* mc_ptr /*nullable*/, const 
                       int rank, int nranks, long long offset, long long count, float scale,
                       int nblocks, int channel, void* stream);
 /* SyncReplicas parameter-server step (C1): owners (ranks < num_ps) average their gradient slice
- * over all workers, apply L2 + momentum-SGD to master/mom and push bf16 weights to all workers */
-int drn_ps_update(const void* const* grads, const void* const* shadows, float* master, float* mom,
-                  const float* hyper, int rank, int nranks, int num_ps, long long offset,
-                  long long count, const void* const* pads, float* l2_sum, int nblocks, int channel,
-                  void* stream);
-/* copy root's buffer into every rank's buffer (BroadcastGlobalVariablesHook, C3) */
-int drn_bcast_f32(const void* const* bufs, const void* const* pads, int rank, int nranks, int root,
-                  long long count, int nblocks, int channel, void* stream);
+ * over all workers, apply L2 + momentum-SGD to master/mom and hand the new bf16 weights to all workers.
+ *   mc_grads  multicast address of the gradient arena or NULL: with it the N copies are added inside
+ *             the switch (multimem.ld_reduce) and cleared with one multimem.st
+ *   want_l2   every owner adds its share of sum(w^2) into the l2 slot of EVERY rank's pad
+ *             (drn_comm_pad_offset(2); zero it at the start of the step)
+ *   pull = 0  the owner pushes the weights into every working arena and the call ends with a barrier
+ *   pull = 1  the weights stay in the owner's arena; the owner publishes epoch ready[bucket][owner]
+ *             in every rank's pad instead - consumers fetch them (drn_conv_igemm_pull,
+ *             drn_ps_sync_vectors).  bucket in [0, 64); offset % 8 == 0. */
+int drn_ps_update(const void* const* grads, void* mc_grads /*nullable*/, const void* const* shadows,
+                  float* master, float* mom, const float* hyper, int rank, int nranks, int num_ps,
+                  long long offset, long long count, const void* const* pads, int want_l2, int pull,
+                  int bucket, int nblocks, int channel, void* stream);
+/* elements per shard owner of a bucket of `count` elements (multiple of 8) */
+long long drn_shard_per(long long count, int num_ps);
+/* One-shot allreduce fused with the optimizer, for small buckets (C2 + K19): every rank reduces the
+ * WHOLE range from all ranks (multimem.ld_reduce when mc_grads is given), applies 1/N, L2 and
+ * momentum-SGD to its own master/mom/shadow and clears its own gradients after a second barrier. */
+int drn_allreduce_sgd_oneshot(const void* const* grads, void* mc_grads /*nullable*/, float* master,
+                              float* mom, void* shadow_bf16, const float* hyper, int rank, int nranks,
+                              long long offset, long long count, const void* const* pads,
+                              float* l2_sum /*nullable*/, int nblocks, int channel, void* stream);
+/* copy root's buffer into every rank's buffer (BroadcastGlobalVariablesHook, C3); with mc_ptr the
+ * root issues one multimem.st per vector and the switch replicates it */
+int drn_bcast_f32(const void* const* bufs, void* mc_ptr /*nullable*/, const void* const* pads, int rank,
+                  int nranks, int root, long long count, int nblocks, int channel, void* stream);
+/* fp32 copies of the vector variables (BatchNorm gamma/beta, dense bias) from the bf16 working arena.
+ * table = device {int64 elem_off; int32 count; int32 map}[n_entries]; maps = device
+ * {int64 lo; int64 per; int32 num_ps; int32 bucket}[]; pull = 1 fetches them from the shard owners
+ * (after waiting for the shards' epochs) and refreshes the local working arena as well. */
+int drn_ps_sync_vectors(const void* const* shadows, void* local_shadow, float* dst_f32,
+                        const void* table, int n_entries, const void* maps, const void* my_pad,
+                        int rank, int nranks, int pull, void* stream);
+/* byte offsets inside a pad: 0 = ready[64][16] uint32, 1 = epoch[64] uint32, 2 = l2 float */
+int drn_comm_pad_offset(int which);
 int drn_comm_barrier(const void* const* pads, int rank, int nranks, int channel, void* stream);
 /* start-up only; these two allocate / map device memory (CUDA IPC fallback for symmetric memory) */
 int drn_ipc_alloc(size_t bytes, void** out_ptr, void* out_handle64);

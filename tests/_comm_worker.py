@@ -106,36 +106,64 @@ def main():
     imgs = torch.from_numpy(rng.integers(0, 256, size=(B, 3072), dtype=np.uint8)).pin_memory()
     labs = torch.from_numpy(rng.integers(0, 10, size=(B,), dtype=np.int32)).pin_memory()
     results = {}
-    for mode in ("allreduce", "ps"):
-        comm = (AllreduceReducer(rank, world, dev, provider=provider) if mode == "allreduce"
-                else ParameterServerReducer(rank, world, dev, num_ps=max(1, world - 1) if world > 2 else world,
-                                            provider=provider))
-        tr = NativeTrainer(spec, B, device=dev, weight_decay=2e-4, comm=comm, use_graph=(mode == "allreduce"))
+    has_mc = bool(red.grad_buf.multicast_ptr)
+    modes = ["allreduce", "allreduce_oneshot", "allreduce_oneshot_p2p", "allreduce_nccl", "ps", "ps_p2p", "ps_pull"]
+    for mode in modes:
+        nps = max(1, world - 1) if world > 2 else world
+        if mode.startswith("allreduce"):
+            algo = {"allreduce": "twoshot", "allreduce_oneshot": "oneshot", "allreduce_oneshot_p2p": "oneshot_p2p",
+                    "allreduce_nccl": "nccl"}[mode]
+            comm = AllreduceReducer(rank, world, dev, provider=provider, algo=algo)
+        else:
+            comm = ParameterServerReducer(rank, world, dev, num_ps=nps, provider=provider,
+                                          algo="p2p" if mode == "ps_p2p" else "auto",
+                                          pull="pull" if mode == "ps_pull" else "push")
+        is_ps = mode.startswith("ps")
+        tr = NativeTrainer(spec, B, device=dev, weight_decay=2e-4, comm=comm,
+                           use_graph=mode in ("allreduce", "allreduce_oneshot", "ps_pull"))
         tr.import_variables(variables)
         m = tr.train_step(imgs, labs, lr=0.1)
         torch.cuda.synchronize(); dist.barrier()
-        if mode == "ps":
+        if is_ps:
             comm.gather_master(tr.engine)
         w = tr.engine.master.clone()      # after ONE step (atomics make later steps diverge chaotically)
         for _ in range(2):
             m = tr.train_step(imgs, labs, lr=0.1)
         torch.cuda.synchronize(); dist.barrier()
-        if mode == "ps":
+        if is_ps:
             comm.gather_master(tr.engine)
+        if mode == "ps_pull":
+            # the working arena of a replica is completed by the forward pass that consumes it
+            tr.engine.forward(training=False)
+            torch.cuda.synchronize(); dist.barrier()
         sh = tr.engine.shadow.float().clone()
         # identical weights on every rank
         for t, name in ((sh, "shadow"), (tr.engine.master.clone(), "master")):
             ref = t.clone(); dist.broadcast(ref, 0)
             assert torch.equal(ref, t), f"{mode}: {name} differs between ranks"
+        assert torch.equal(sh, tr.engine.master.bfloat16().float()), f"{mode}: working copy != bf16(master)"
+        if is_ps:
+            # every replica computes with the same gamma / beta / bias: the fp32 image of the working copy
+            if mode != "ps_pull":
+                comm.sync_vectors(tr.engine); torch.cuda.synchronize()
+            e = tr.engine
+            for name in ("batch_normalization/gamma", "batch_normalization_3/beta", "dense/bias"):
+                ent = e.layout.entries[name]
+                got = e.vec_f32[ent.offset:ent.offset + ent.numel]
+                assert torch.equal(got, e.master[ent.offset:ent.offset + ent.numel].bfloat16().float()), (mode, name)
+            assert abs(m["cost"] - m["cross_entropy"]) > 1e-3, f"{mode}: L2 term missing from the cost"
         results[mode] = w
         assert np.isfinite(m["cost"])
         if rank == 0:
-            print(f"{mode}: 3 steps ok, cost={m['cost']:.4f}", flush=True)
-    # the two transports implement the same mathematics
-    diff = (results["allreduce"] - results["ps"]).abs().max().item()
-    if rank == 0:
-        print(f"allreduce-vs-ps max weight diff after one step: {diff:.3e}", flush=True)
-    assert diff < 1e-3, ("allreduce vs ps weights after one step", diff)
+            print(f"{mode}: 3 steps ok, cost={m['cost']:.4f} xent={m['cross_entropy']:.4f}"
+                  f" multicast={comm.use_multicast()}", flush=True)
+        del tr, comm
+    # all transports implement the same mathematics
+    for mode in modes[1:]:
+        diff = (results["allreduce"] - results[mode]).abs().max().item()
+        if rank == 0:
+            print(f"allreduce-vs-{mode} max weight diff after one step: {diff:.3e}", flush=True)
+        assert diff < 1e-3, ("allreduce vs " + mode + " weights after one step", diff)
 
     # single-replica reference: mean of the per-replica gradients applied once
     tr1 = NativeTrainer(spec, B, device=dev, weight_decay=2e-4, comm=None, use_graph=False)
