@@ -132,7 +132,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="native", choices=["native", "reference", "torch_baseline"])
+    ap.add_argument("--impl", default="native", choices=["native", "reference", "torch_baseline", "torch_tuned"])
     ap.add_argument("--model", default="imagenet", choices=["imagenet", "cifar10"])
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default 128; CIFAR: 128/N)")
     ap.add_argument("--resnet_size", type=int, default=50)
@@ -222,6 +222,34 @@ def main():
             last["prev"] = m
 
         h2d, d2h = tr.h2d_bytes_per_step, tr.d2h_bytes_per_step
+    elif args.impl == "torch_tuned":
+        # tuned stock PyTorch: channels_last + bf16 autocast + fused SGD + DDP + whole-step CUDA graph
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        from torch_tuned import TorchTuned
+        tt = TorchTuned(spec, B, device, wd, world, graph=not args.no_graph)
+        tt.prepare()
+        dev_batches = [(host_imgs[i].to(device), host_labs[i].to(device).long()) for i in range(2)]
+        host_labs64 = [h.long().pin_memory() for h in host_labs]
+
+        def device_step(i):
+            tt.load(*dev_batches[i & 1])
+            tt.step()
+
+        last = {}
+        loss_pin = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+
+        def e2e_step(i):
+            tt.load(host_imgs[i % n_host], host_labs64[i % n_host])
+            loss = tt.step()
+            if "ev" in last:                               # D2H read of the previous step's loss
+                last["ev"].synchronize()
+                last["metrics"] = {"cross_entropy": float(loss_pin[last["slot"]]), "cuda_graph": tt.graphed}
+            loss_pin[i & 1].copy_(loss, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            last["ev"], last["slot"] = ev, i & 1
+
+        h2d, d2h = B * img_hw * img_hw * 3 + B * 8, 4
     else:
         sys.path.insert(0, os.path.join(ROOT, "baseline"))
         from torch_baseline import TorchBaseline

@@ -18,15 +18,34 @@ def main(n=1024, batch=128):
         buf = io.BytesIO(); Image.fromarray(img).save(buf, format="JPEG", quality=90)
         recs.append(make_example({"image/encoded": [buf.getvalue()], "image/class/label": [i % 1000 + 1]}))
     d = tempfile.mkdtemp(); shard = os.path.join(d, "train-00000-of-01024"); write_tfrecords(shard, recs)
+    shards = []
+    for j in range(8):                 # the same records spread over 8 shards for the reader processes
+        f = os.path.join(d, "train-%05d-of-01024" % (j + 1)); write_tfrecords(f, recs[j::8] * 4); shards.append(f)
     print(f"{n} JPEGs, {sum(len(r) for r in recs) / n / 1024:.0f} KiB each")
-    for name, cls, kw in (("host", im.ImageNetBatches, {}), ("device", im.ImageNetBatchesGPU, {"device": "cuda:0"})):
-        it = iter(cls(d, batch, True, 2, seed=1, files=[shard], **kw))
-        next(it)                      # warm-up (thread pool, nvJPEG handles)
+    import torch
+    ncpu = os.cpu_count() or 1
+    print(f"host cores: {ncpu}")
+    arms = [("host, 5 threads (reference's num_threads=5)", im.ImageNetBatches, {}),
+            (f"host, {min(8, ncpu)} reader processes x 5 threads", im.MultiProcessBatches, {"workers": min(8, ncpu)}),
+            ("device, torchvision nvJPEG binding", im.ImageNetBatchesGPU, {"device": "cuda:0", "decoder": "torchvision"}),
+            ("device, libdrn nvJPEG binding (csrc/jpeg.cu)", im.ImageNetBatchesGPU, {"device": "cuda:0", "decoder": "native"})]
+    for name, cls, kw in arms:
+        try:
+            obj = cls(d, batch, True, 3, seed=1, files=[shard] if cls is not im.MultiProcessBatches else shards, **kw)
+        except Exception as e:
+            print(f"{name}: unavailable ({e!r})"); continue
+        it = iter(obj)
+        next(it)                      # warm-up (thread pool, nvJPEG handles, process start)
+        torch.cuda.synchronize()
         t0 = time.time(); k = 0
         for b in it:
             k += len(b[1])
+        torch.cuda.synchronize()
         dt = time.time() - t0
-        print(f"{name:6s}: {k / dt:8.0f} images/s ({k} images in {dt:.2f} s)", flush=True)
+        extra = f" [{obj.decoder_name}]" if hasattr(obj, "decoder_name") else ""
+        print(f"{name}{extra}: {k / dt:8.0f} images/s ({k} images in {dt:.2f} s)", flush=True)
+        if hasattr(obj, "close"):
+            obj.close()
 
 if __name__ == "__main__":
     main()

@@ -293,6 +293,72 @@ __global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8*
   }
 }
 
+// Post-activation (v1) blocks: out = relu(bn(y) + shortcut).  Backward of the ReLU plus the two
+// reductions the following BatchNorm backward needs, for up to two BatchNorms that feed the same
+// sum (the main path's last BN and the projection shortcut's BN):
+//   dm = g * [out > 0];  stats += (sum dm, sum dm*y);  stats2 += (sum dm, sum dm*y2)   (y2 optional)
+__global__ void relu_bwd_reduce_kernel(const BF8* __restrict__ g, const BF8* __restrict__ out,
+                                       const BF8* __restrict__ y, const BF8* __restrict__ y2,
+                                       BF8* __restrict__ dm, float* __restrict__ stats,
+                                       float* __restrict__ stats2, int stats_ld, long long M, int c8) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ float s_acc[kThreads * 24];
+  const int cg = threadIdx.x % c8;
+  const int pl = threadIdx.x / c8;
+  const int lanes = kThreads / c8;
+  float s1[8], s2[8], s3[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s1[k] = s2[k] = s3[k] = 0.f;
+  const long long step = (long long)gridDim.x * lanes;
+  for (long long m = (long long)blockIdx.x * lanes + pl; m < M; m += step) {
+    const long long i = m * c8 + cg;
+    const BF8 gv = g[i], ov = out[i], yv = y[i];
+    float gf[8], of[8], yf[8];
+    unpack8(gv, gf);
+    unpack8(ov, of);
+    unpack8(yv, yf);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) gf[k] = of[k] > 0.f ? gf[k] : 0.f;
+    const BF8 packed = pack8(gf);
+    dm[i] = packed;
+    float gq[8];
+    unpack8(packed, gq);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      s1[k] += gq[k];
+      s2[k] = fmaf(gq[k], yf[k], s2[k]);
+    }
+    if (y2 != nullptr) {
+      float y2f[8];
+      unpack8(y2[i], y2f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s3[k] = fmaf(gq[k], y2f[k], s3[k]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    s_acc[threadIdx.x * 24 + k] = s1[k];
+    s_acc[threadIdx.x * 24 + 8 + k] = s2[k];
+    s_acc[threadIdx.x * 24 + 16 + k] = s3[k];
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < c8 * 24; t += blockDim.x) {
+    const int grp = t / 24, k = t % 24;
+    float a = 0.f;
+    for (int l = 0; l < lanes; ++l) a += s_acc[(l * c8 + grp) * 24 + k];
+    const int c = grp * 8 + (k & 7);
+    if (k < 8) {
+      atomicAdd(stats + c, a);
+      if (stats2 != nullptr) atomicAdd(stats2 + c, a);
+    } else if (k < 16) {
+      atomicAdd(stats + stats_ld + c, a);
+    } else if (stats2 != nullptr) {
+      atomicAdd(stats2 + stats_ld + c, a);
+    }
+  }
+}
+
 // dgamma, dbeta and the coefficients of dy = A*dm + B*y + C
 __global__ void bn_bwd_finalize_kernel(const float* __restrict__ stats, int stats_ld,
                                        float inv_count, const float* __restrict__ gamma,
@@ -673,6 +739,22 @@ extern "C" int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int ad
   DRN_CHECK_CUDA(launch_pdl(kern, dim3((int)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
                             (const BF8*)da, (const BF8*)addend, H, W, Ha, Wa, bcast_scale, (const BF8*)y,
                             (const float2*)scale_shift, (BF8*)dm, stats, stats_ld, M, C / 8));
+  return 0;
+}
+
+// v1 (post-activation) residual blocks: backward of out = relu(bn(y) + shortcut), see the kernel.
+extern "C" int drn_relu_bwd_reduce(const void* g, const void* out, const void* y, const void* y2,
+                                   void* dm, float* stats, float* stats2, int stats_ld, long long M,
+                                   int C, void* stream) {
+  if (int e = check_c(C, "relu_bwd_reduce")) return e;
+  DRN_REQUIRE((y2 == nullptr) == (stats2 == nullptr), "relu_bwd_reduce: y2 and stats2 go together");
+  const int lanes = kThreads / (C / 8);
+  long long blocks = (M + lanes - 1) / lanes;
+  const long long cap = (long long)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  DRN_CHECK_CUDA(launch_pdl(relu_bwd_reduce_kernel, dim3((int)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)g, (const BF8*)out, (const BF8*)y, (const BF8*)y2, (BF8*)dm, stats,
+                            stats2, stats_ld, M, C / 8));
   return 0;
 }
 

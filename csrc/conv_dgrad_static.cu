@@ -11,7 +11,11 @@
 //
 // What to know before using it:
 //   * The array is DRN_DGRAD_STATIC_SCRATCH_BYTES (16 MiB) and is reserved on every GPU whose
-//     context loads this library, whether or not the function is ever called.
+//     context loads this library's device code, whether or not the function is ever called.  With
+//     CUDA's default lazy module loading that reservation happens when the first kernel of the
+//     library runs on the device (or at this function's first call) - not at dlopen.  A host pool
+//     that grabs "all remaining memory" must therefore be created AFTER that first call, otherwise
+//     the reservation itself can fail with an out-of-memory error.
 //   * Problems whose zero-inserted dy ( 2 * N * ((P-1)*stride+1) * ((Q-1)*stride+1) * K bytes,
 //     see drn_conv_dgrad_scratch_bytes ) does not fit are refused with an error; use
 //     drn_conv_dgrad with your own buffer for those.
@@ -27,6 +31,8 @@
 // This entry point has no counterpart in the reference.
 #include <cuda_runtime.h>
 
+#include <atomic>
+
 #include "host.cuh"
 #include "../include/drn_b200.h"
 
@@ -35,7 +41,9 @@ namespace {
 static __device__ __align__(256) unsigned char g_dgrad_scratch[DRN_DGRAD_STATIC_SCRATCH_BYTES];
 
 constexpr int kMaxDevices = 64;
-void* g_scratch_addr[kMaxDevices] = {nullptr};  // device address of g_dgrad_scratch, per device
+// device address of g_dgrad_scratch, per device; host threads may race to fill an entry (they all
+// store the same value), hence atomics
+std::atomic<void*> g_scratch_addr[kMaxDevices];
 
 // In host code `g_dgrad_scratch` is only a handle for the runtime, not a device address: the real
 // address differs per device and has to be asked for with that device current.
@@ -43,13 +51,13 @@ int scratch_for_current_device(void** out) {
   int dev = -1;
   DRN_CHECK_CUDA(cudaGetDevice(&dev));
   DRN_REQUIRE(dev >= 0 && dev < kMaxDevices, "conv_dgrad_static: device ordinal %d out of range", dev);
-  if (g_scratch_addr[dev] == nullptr) {
-    void* p = nullptr;
+  void* p = g_scratch_addr[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {
     DRN_CHECK_CUDA(cudaGetSymbolAddress(&p, g_dgrad_scratch));
     DRN_REQUIRE(p != nullptr, "conv_dgrad_static: cudaGetSymbolAddress returned a null address");
-    g_scratch_addr[dev] = p;
+    g_scratch_addr[dev].store(p, std::memory_order_release);
   }
-  *out = g_scratch_addr[dev];
+  *out = p;
   return 0;
 }
 

@@ -81,7 +81,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     if LIB.exists() and LIB.stat().st_mtime >= newest and not force:
         return LIB
     cmd = [_nvcc(), *ARCH_FLAGS, "-shared", "-Xcompiler", "-fPIC", "-o", str(LIB),
-           *[str(o) for o in objs], "-lcudart"]
+           *[str(o) for o in objs], "-lcudart", "-lnvjpeg", "-Xlinker", "-rpath", "-Xlinker", "/usr/local/cuda/lib64"]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")

@@ -71,6 +71,7 @@ _SIGNATURES = {
     "drn_bn_apply": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp]),
     "drn_bn_stats": (_i, [_vp, _vp, _i, _ll, _i, _vp]),
     "drn_bn_bwd_mask_reduce": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "drn_relu_bwd_reduce": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _vp]),
     "drn_bn_bwd_finalize": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "drn_bn_bwd_apply": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _i, _vp]),
     "drn_maxpool_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
@@ -86,6 +87,11 @@ _SIGNATURES = {
     "drn_cifar_augment": (_i, [_vp, _i, _i, _vp, _i, _i, _i, ctypes.c_ulonglong, ctypes.c_uint, _ll, _i, _vp]),
     "drn_imagenet_prep": (_i, [_vp, _ll, _i, _i, _vp, _vp, _i, _i, _f, _f, _f, _i, _i, _vp]),
     "drn_resize_bilinear": (_i, [_vp, _i, _i, _vp, _i, _i, _vp]),
+    "drn_jpeg_create": (_i, [_i, ctypes.POINTER(_vp)]),
+    "drn_jpeg_backend": (_i, [_vp]),
+    "drn_jpeg_destroy": (_i, [_vp]),
+    "drn_jpeg_info": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "drn_jpeg_decode_batch": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _vp, _vp]),
     "drn_crc32c": (ctypes.c_uint32, [_vp, ctypes.c_size_t, ctypes.c_uint32]),
     "drn_tfrecord_index": (_ll, [_vp, ctypes.c_size_t, _vp, _vp, _ll, _i]),
     "drn_comm_pad_bytes": (_i, []),

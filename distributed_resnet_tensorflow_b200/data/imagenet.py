@@ -108,7 +108,14 @@ class ImageNetBatches:
 
 
 def gpu_decode_available() -> bool:
-    """True when torchvision can decode JPEG batches on the GPU (nvJPEG)."""
+    """True when JPEG batches can be decoded on the GPU: the library's own nvJPEG binding
+    (csrc/jpeg.cu) or, failing that, torchvision's."""
+    try:
+        from . import jpeg_native
+        if jpeg_native.available():
+            return True
+    except Exception:  # pragma: no cover
+        pass
     try:
         import torch
         import torchvision  # noqa: F401
@@ -134,11 +141,54 @@ class ImageNetBatchesGPU(ImageNetBatches):
 
     def __init__(self, data_dir: str, batch_size: int, training: bool, num_epochs: Optional[int] = None,
                  seed: int = 0, num_threads: int = 5, files: Optional[List[str]] = None,
-                 device: str = "cuda:0", out_hw: int = 224):
+                 device: str = "cuda:0", out_hw: int = 224, decoder: str = "auto", decode_threads: int = 3):
         super().__init__(data_dir, batch_size, training, num_epochs, seed, num_threads, files)
+        import threading
         import torch
         self.device = torch.device(device)
         self.out_hw = out_hw
+        self.native = None
+        self._tls = threading.local()
+        # whole batches are decoded concurrently by `decode_threads` workers, each with its own nvJPEG
+        # decoder and CUDA stream (the nvJPEG calls release the GIL); results are yielded in order
+        self.decode_threads = max(1, decode_threads)
+        if decoder in ("auto", "native"):
+            try:
+                from .jpeg_native import NativeJpegDecoder, available
+                if available():
+                    self.native = NativeJpegDecoder(self.device)
+            except Exception:
+                if decoder == "native":
+                    raise
+        if self.native is None:
+            self.decode_threads = 1
+        self.decoder_name = self.native.backend if self.native is not None else "torchvision nvJPEG binding"
+
+    def _thread_decoder(self):
+        d = getattr(self._tls, "dec", None)
+        if d is None:
+            import torch
+            from .jpeg_native import NativeJpegDecoder
+            d = self._tls.dec = NativeJpegDecoder(self.device)
+            self._tls.stream = torch.cuda.Stream(device=self.device)
+        return d
+
+    def _decode_native(self, items):
+        """csrc/jpeg.cu: one nvJPEG batch -> planar RGB planes in one device arena."""
+        import torch
+        arena, offsets, wh, status = self._thread_decoder().decode([enc for enc, _, _ in items])
+        base = arena.data_ptr()
+        ptr_list, dims, keep = [], [], []
+        for i, (enc, _, _) in enumerate(items):
+            if status[i] == 0:
+                ptr_list.append(base + int(offsets[i]))
+                dims.append((int(wh[i, 1]), int(wh[i, 0])))
+            else:       # not decodable on the GPU (CMYK, PNG in disguise, ...): host decoder, then upload
+                t = torch.from_numpy(decode_image(enc)).permute(2, 0, 1).contiguous().to(self.device)
+                keep.append(t)
+                ptr_list.append(t.data_ptr())
+                dims.append((int(t.shape[1]), int(t.shape[2])))
+        return ptr_list, dims, keep
 
     def _encoded(self) -> Iterator[Tuple[bytes, int, int]]:
         """(jpeg bytes, label, per-example seed) in file order (shuffled shard list when training)."""
@@ -154,29 +204,42 @@ class ImageNetBatchesGPU(ImageNetBatches):
 
     def _decode_batch(self, items):
         import torch
-        from torchvision.io import ImageReadMode, decode_jpeg
+        if self.native is not None:
+            self._thread_decoder()
+            with torch.cuda.stream(self._tls.stream):
+                return self._decode_batch_on_stream(items)
+        return self._decode_batch_on_stream(items)
+
+    def _decode_batch_on_stream(self, items):
+        import torch
         from .._native import lib as _nl
+        if self.native is None:
+            from torchvision.io import ImageReadMode, decode_jpeg
         B = len(items)
-        bufs = [torch.frombuffer(bytearray(enc), dtype=torch.uint8) for enc, _, _ in items]
-        try:
-            imgs = decode_jpeg(bufs, device=self.device, mode=ImageReadMode.RGB)
-        except Exception:
-            imgs = []
-            for (enc, _, _), b in zip(items, bufs):
-                try:
-                    imgs.append(decode_jpeg(b, device=self.device, mode=ImageReadMode.RGB))
-                except Exception:   # not a baseline/progressive RGB or grey JPEG: host decoder
-                    imgs.append(torch.from_numpy(decode_image(enc)).permute(2, 0, 1).contiguous().to(self.device))
-        imgs = [im.contiguous() for im in imgs]
+        if self.native is not None:
+            ptr_list, dims, imgs = self._decode_native(items)
+        else:
+            bufs = [torch.frombuffer(bytearray(enc), dtype=torch.uint8) for enc, _, _ in items]
+            try:
+                imgs = decode_jpeg(bufs, device=self.device, mode=ImageReadMode.RGB)
+            except Exception:
+                imgs = []
+                for (enc, _, _), b in zip(items, bufs):
+                    try:
+                        imgs.append(decode_jpeg(b, device=self.device, mode=ImageReadMode.RGB))
+                    except Exception:   # not a baseline/progressive RGB or grey JPEG: host decoder
+                        imgs.append(torch.from_numpy(decode_image(enc)).permute(2, 0, 1).contiguous().to(self.device))
+            imgs = [im.contiguous() for im in imgs]
+            ptr_list = [im.data_ptr() for im in imgs]
+            dims = [(int(im.shape[1]), int(im.shape[2])) for im in imgs]
         meta = np.zeros((B, 6), np.int32)
         flips = np.zeros(B, np.int32)
-        for i, ((_, _, seed), im) in enumerate(zip(items, imgs)):
-            h, w = int(im.shape[1]), int(im.shape[2])
+        for i, ((_, _, seed), (h, w)) in enumerate(zip(items, dims)):
             nh, nw, oy, ox, flip = preprocess.vgg_crop_params(h, w, self.training, self.out_hw,
                                                               np.random.default_rng(seed))
             meta[i] = (h, w, nh, nw, oy, ox)
             flips[i] = flip
-        ptrs = torch.tensor([im.data_ptr() for im in imgs], dtype=torch.int64).to(self.device)
+        ptrs = torch.tensor(ptr_list, dtype=torch.int64).to(self.device)
         dmeta = torch.from_numpy(meta).to(self.device)
         out = torch.empty((B, self.out_hw * self.out_hw * 3), dtype=torch.uint8, device=self.device)
         with torch.cuda.device(self.device):
@@ -187,7 +250,7 @@ class ImageNetBatchesGPU(ImageNetBatches):
         crop = np.stack([np.zeros(B, np.int32), np.zeros(B, np.int32), flips], 1).astype(np.int32)
         return out, labs, crop
 
-    def __iter__(self):
+    def _encoded_batches(self):
         buf: List[Tuple[bytes, int, int]] = []
         out: List[Tuple[bytes, int, int]] = []
         cap = SHUFFLE_BUFFER if self.training else 1
@@ -198,14 +261,97 @@ class ImageNetBatchesGPU(ImageNetBatches):
                 buf[i], buf[-1] = buf[-1], buf[i]
                 out.append(buf.pop())
                 if len(out) == self.B:
-                    yield self._decode_batch(out)
+                    yield out
                     out = []
         if self.training:
             self.rng.shuffle(buf)
         for ex in buf:
             out.append(ex)
             if len(out) == self.B:
-                yield self._decode_batch(out)
+                yield out
                 out = []
         if out:
-            yield self._decode_batch(out)
+            yield out
+
+    def __iter__(self):
+        if self.decode_threads <= 1:
+            for items in self._encoded_batches():
+                yield self._decode_batch(items)
+            return
+        from collections import deque
+        pool = ThreadPoolExecutor(max_workers=self.decode_threads)
+        pending = deque()
+        try:
+            for items in self._encoded_batches():
+                pending.append(pool.submit(self._decode_batch, items))
+                if len(pending) > self.decode_threads:
+                    yield pending.popleft().result()
+            while pending:
+                yield pending.popleft().result()
+        finally:
+            pool.shutdown(wait=False)
+
+
+# ------------------------------------------------------------------------------------------------
+# reader processes
+# ------------------------------------------------------------------------------------------------
+def _reader_process(q, data_dir, batch_size, training, num_epochs, seed, num_threads, files):
+    try:
+        it = ImageNetBatches(data_dir, batch_size, training, num_epochs, seed, num_threads, files)
+        for batch in it:
+            q.put(batch)
+        q.put(None)
+    except BaseException as e:   # surfaced in the consumer
+        q.put(e)
+
+
+class MultiProcessBatches:
+    """``workers`` reader processes, each running the host pipeline (TFRecord -> tf.Example -> JPEG
+    decode -> VGG resize/crop) over its own share of the shard files with its own shuffle stream;
+    batches are taken from the processes in turn.  One Python process decodes ~1 000 images/s with
+    five threads (the reference's ``num_threads=5``, resnet_imagenet_main.py:166-168) and a B200
+    consumes fifteen times that, so the host path needs processes, not threads, to scale with cores.
+    ``--input_workers`` selects the count."""
+
+    def __init__(self, data_dir: str, batch_size: int, training: bool, num_epochs: Optional[int] = None,
+                 seed: int = 0, workers: int = 4, num_threads: int = 5, files: Optional[List[str]] = None,
+                 depth: int = 3):
+        import multiprocessing as mp
+        files = files if files is not None else [f for f in filenames(training, data_dir) if os.path.exists(f)]
+        if not files:
+            raise FileNotFoundError(f"no ImageNet TFRecord shards under {data_dir!r}")
+        workers = max(1, min(workers, len(files)))
+        ctx = mp.get_context("spawn")
+        self._procs, self._queues = [], []
+        for w in range(workers):
+            q = ctx.Queue(maxsize=depth)
+            p = ctx.Process(target=_reader_process, daemon=True,
+                            args=(q, data_dir, batch_size, training, num_epochs, seed + 7919 * w, num_threads,
+                                  files[w::workers]))
+            p.start()
+            self._procs.append(p)
+            self._queues.append(q)
+
+    def __iter__(self):
+        live = list(range(len(self._queues)))
+        while live:
+            for w in list(live):
+                item = self._queues[w].get()
+                if item is None:
+                    live.remove(w)
+                    continue
+                if isinstance(item, BaseException):
+                    self.close()
+                    raise item
+                yield item
+
+    def close(self) -> None:
+        for p in self._procs:
+            if p.is_alive():
+                p.terminate()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass

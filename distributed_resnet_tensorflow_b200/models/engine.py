@@ -232,9 +232,9 @@ class NativeResNet:
     def __init__(self, spec: NetSpec, batch: int, device="cuda:0", storage: Optional[dict] = None):
         """``storage`` may supply pre-allocated ``grad`` (fp32) / ``shadow`` (bf16) arenas of at
         least ``ParamLayout(spec).total`` elements - the collectives need them in symmetric memory."""
-        if spec.version != 2:
-            raise NotImplementedError("the native engine implements the reference's v2 networks; "
-                                      "use --backend=torch for resnet_version=1")
+        if spec.version != 2 and type(self) is NativeResNet:
+            raise ValueError("post-activation (v1) networks run on models.engine_v1.NativeResNetV1; "
+                             "use models.engine.make_engine(spec, ...)")
         _nl.load()
         self.spec = spec
         self.B = batch
@@ -562,20 +562,20 @@ class NativeResNet:
             _nl.call("drn_bn_inference_params", _p(bn.gamma), _p(bn.beta), _p(bn.run_mean),
                      _p(bn.run_var), BN_EPS, _p(bn.ss), bn.C, st)
 
-    def _bn_fwd(self, bn: _BN, y, out, training: bool):
+    def _bn_fwd(self, bn: _BN, y, out, training: bool, relu: bool = True):
         """a = relu(bn(y)): statistics -> scale/shift -> apply, one launch in training mode."""
         count = y.numel() // bn.C
         if training:
             _nl.call("drn_bn_finalize_apply", _p(y), _p(bn.fstats), bn.fstats.stride(0), count, _p(bn.gamma),
                      _p(bn.beta), _p(bn.run_mean), _p(bn.run_var), BN_DECAY, BN_EPS, _p(bn.ss), _p(bn.mi),
-                     _p(out), bn.C, 1, self._st())
+                     _p(out), bn.C, 1 if relu else 0, self._st())
         else:
             self._bn_finalize(bn, count, False)
-            self._bn_apply(bn, y, out)
+            self._bn_apply(bn, y, out, relu=relu)
 
-    def _bn_apply(self, bn: _BN, y, out):
+    def _bn_apply(self, bn: _BN, y, out, addend=None, relu: bool = True):
         M = y.numel() // bn.C
-        _nl.call("drn_bn_apply", _p(y), _p(bn.ss), 0, _p(out), M, bn.C, 1, self._st())
+        _nl.call("drn_bn_apply", _p(y), _p(bn.ss), _p(addend), _p(out), M, bn.C, 1 if relu else 0, self._st())
 
     def _dgrad(self, conv: _Conv, dy, out, side=None, stats=None, ss=None, mode=EPI_PLAIN):
         """Data gradient of ``conv`` given dy; writes [B, H, W, Cin] into ``out``. Strided
@@ -878,3 +878,12 @@ class NativeResNet:
         self.loss(with_grad=True)
         self.backward()
         self.apply_gradients()
+
+
+def make_engine(spec: NetSpec, batch: int, device="cuda:0", storage: Optional[dict] = None):
+    """Native executor for ``spec``: pre-activation (v2, the reference's networks) or
+    post-activation (v1, the north-star's extra family)."""
+    if spec.version == 1:
+        from .engine_v1 import NativeResNetV1
+        return NativeResNetV1(spec, batch, device=device, storage=storage)
+    return NativeResNet(spec, batch, device=device, storage=storage)

@@ -90,17 +90,17 @@ def init_process_group(cfg: Config, ctx: DistContext, device_type: str) -> None:
 # data
 # ------------------------------------------------------------------------------------------------
 def use_gpu_decode(cfg: Config, device: Optional[str]) -> bool:
-    """--input_decode=gpu needs a CUDA device and torchvision's nvJPEG binding.  `auto` stays on the
-    host path: measured on the B200 box (bench/bench_input.py, 500x375 JPEGs) the two paths deliver
-    the same ~1 000 images/s per process (torchvision's nvJPEG binding still Huffman-decodes on one
-    host thread); the device path frees four CPU threads per rank, which matters at 8 ranks per node."""
+    """--input_decode: `gpu` needs a CUDA device and a GPU JPEG decoder (the library's nvJPEG binding,
+    csrc/jpeg.cu, or torchvision's); `auto` takes the device path whenever that is available - JPEG
+    decode, VGG resize and crop then run on the GPU (drn_jpeg_decode_batch + drn_resize_crop_batch)
+    and the host only parses records; `cpu` is the reference's host pipeline."""
     mode = cfg.train.input_decode
-    if mode != "gpu" or device is None or not str(device).startswith("cuda"):
+    if mode == "cpu" or device is None or not str(device).startswith("cuda"):
         return False
     from ..data.imagenet import gpu_decode_available
     ok = gpu_decode_available()
     if mode == "gpu" and not ok:
-        raise RuntimeError("--input_decode=gpu needs torchvision with CUDA JPEG decoding")
+        raise RuntimeError("--input_decode=gpu needs the library's nvJPEG binding or torchvision with CUDA JPEG decoding")
     return ok
 
 
@@ -113,6 +113,10 @@ def training_batches(cfg: Config, spec: NetSpec, ctx: DistContext, device: Optio
             if use_gpu_decode(cfg, device):
                 return iter(ImageNetBatchesGPU(cfg.paths.train_data_path, B, True, cfg.train.num_epochs, seed,
                                                device=device))
+            if cfg.train.input_workers > 0:
+                from ..data.imagenet import MultiProcessBatches
+                return iter(MultiProcessBatches(cfg.paths.train_data_path, B, True, cfg.train.num_epochs, seed,
+                                                workers=cfg.train.input_workers))
             return iter(ImageNetBatches(cfg.paths.train_data_path, B, True, cfg.train.num_epochs, seed))
         from ..data.synthetic import synthetic_imagenet_batches
 
@@ -145,7 +149,7 @@ def choose_backend(cfg: Config) -> str:
         has_gpu = torch.cuda.is_available() and cfg.num_gpus > 0
     except Exception:
         has_gpu = False
-    if has_gpu and cfg.model.resnet_version == 2 and cfg.model.model == "resnet" and cfg.train.dtype == "bf16":
+    if has_gpu and cfg.model.model == "resnet" and cfg.train.dtype == "bf16":
         return "native"
     return "torch"
 

@@ -23,7 +23,7 @@ import numpy as np
 import torch
 
 from .._native import lib as _nl
-from ..models.engine import VGG_MEANS, NativeResNet, _p
+from ..models.engine import VGG_MEANS, NativeResNet, _p, make_engine
 from ..models.spec import NetSpec
 
 
@@ -61,7 +61,7 @@ class NativeTrainer:
         if comm is not None:
             from ..models.engine import ParamLayout
             storage = comm.allocate(ParamLayout(spec).total)
-        self.engine = NativeResNet(spec, batch, device=device, storage=storage)
+        self.engine = make_engine(spec, batch, device=device, storage=storage)
         if comm is not None and hasattr(comm, "attach"):
             comm.attach(self.engine)
         self.weight_decay = weight_decay

@@ -254,8 +254,11 @@ EXTENSION_FLAGS: List[FlagDef] = [
     _n("eval_interval_secs", 60, "Evaluator polling period."),
     _n("seed", 0, "Base RNG seed (initialisation is identical on all replicas)."),
     _b("synthetic_data", False, "Force synthetic inputs even if a data path is given."),
-    _s("input_decode", "auto", "ImageNet JPEG decode + resize: cpu (PIL worker threads, as the reference), "
-       "gpu (nvJPEG batch decode + one resize/crop kernel, frees the CPU threads), auto = cpu."),
+    _s("input_decode", "auto", "ImageNet JPEG decode + resize: cpu (PIL on the host, as the reference), "
+       "gpu (nvJPEG batch decode - hardware JPEG engine when present - + one resize/crop kernel), "
+       "auto = gpu when training on a CUDA device with a GPU decoder available."),
+    _n("input_workers", 0, "ImageNet host input path: number of reader PROCESSES (0 = threads in the "
+       "training process, as the reference's num_threads=5)."),
     _b("profile", False, "Print the parameter / FLOP table (tfprof-style) and per-kernel timings."),
     _b("cuda_graph", True, "Capture the training step in a CUDA graph (native backend)."),
     _s("allreduce_algo", "auto", "Gradient allreduce of the Horovod path: auto (one-shot for buckets <= 4 MB "

@@ -127,7 +127,9 @@ int drn_conv_dgrad_s2(const drn_conv_desc* desc, const void* dy, const void* ban
  * e.g. a process that gave the whole GPU to its own memory pool, or a latency-critical loop where
  * cudaMalloc/cudaFree (which synchronise the device) are off limits.  The zero-insertion scratch
  * lives in a fixed DRN_DGRAD_STATIC_SCRATCH_BYTES array inside the library (reserved on every GPU
- * that loads it); larger problems are refused with an error.  The first call on a device resolves
+ * whose context loads the library's device code - with lazy module loading that is the first kernel
+ * launch or this function's first call, so a pool that takes "all remaining memory" must be created
+ * after it); larger problems are refused with an error.  The first call on a device resolves
  * the array's device address - make it at start-up, before any stream capture.  All calls share
  * the array: every call rewrites what it uses, so nothing has to be cleared, but calls that can
  * overlap on the GPU race with each other.  Allocates nothing.  No counterpart in the reference. */
@@ -184,6 +186,12 @@ int drn_bn_stats(const void* y, float* stats, int stats_ld, long long M, int C, 
 int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int addend_kind, int N, int H, int W,
                            int Ha, int Wa, float bcast_scale, const void* y, const void* scale_shift,
                            void* dm, float* stats, int stats_ld, int C, void* stream);
+/* Post-activation (v1) residual blocks, out = relu(bn(y) + shortcut): dm = g * [out > 0],
+ * stats += (sum dm, sum dm*y) and, for a projection shortcut with its own BatchNorm over y2,
+ * stats2 += (sum dm, sum dm*y2) (y2 / stats2 nullable together).  The reference ships v2 only
+ * (resnet_model_official.py:15-29); v1 is the north-star's extra model family. */
+int drn_relu_bwd_reduce(const void* g, const void* out, const void* y, const void* y2, void* dm,
+                        float* stats, float* stats2, int stats_ld, long long M, int C, void* stream);
 /* dgamma += sum dm*xhat, dbeta += sum dm (both nullable), coef = (A,B,C) of dy = A*dm + B*y + C */
 int drn_bn_bwd_finalize(const float* stats, int stats_ld, long long count, const float* gamma,
                         const void* mean_invstd, float* dgamma, float* dbeta, void* coef, int C,
@@ -248,6 +256,19 @@ int drn_resize_bilinear(const void* src, int sh, int sw, float* dst, int dh, int
  * meta = DEVICE int[B][6] {src_h, src_w, new_h, new_w, off_y, off_x}; out = uint8 [B][crop][crop][3]. */
 int drn_resize_crop_batch(const void* src_ptrs, const int* meta, void* out, int B, int crop,
                           void* stream);
+
+/* Batched JPEG decode on the GPU (nvJPEG; hardware engine when the device has one), op K23.  The
+ * reference decodes on five CPU threads (tf.image.decode_jpeg, resnet_imagenet_main.py:138-168).
+ * drn_jpeg_create allocates nvJPEG's internal device/pinned work buffers: call it at start-up.
+ *   data/lengths: HOST arrays of B host pointers / sizes; wh: HOST int[B][2] (width, height);
+ *   out: HOST array of B DEVICE pointers, each uint8 [3][h][w] (planar RGB, the input format of
+ *   drn_resize_crop_batch); status: HOST int[B], 0 = decoded, otherwise use a host decoder. */
+int drn_jpeg_create(int prefer_hardware, void** out_handle);
+int drn_jpeg_backend(void* handle); /* 2 = hardware JPEG engine, 1 = GPU hybrid, 0 = default */
+int drn_jpeg_destroy(void* handle);
+int drn_jpeg_info(void* handle, const unsigned char* const* data, const size_t* lengths, int B, int* wh);
+int drn_jpeg_decode_batch(void* handle, const unsigned char* const* data, const size_t* lengths, int B,
+                          void* const* out, const int* wh, int* status, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Host utilities (no GPU): CRC-32C (Castagnoli) used by TensorBundle checkpoints, TFRecord files

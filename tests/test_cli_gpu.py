@@ -51,7 +51,8 @@ def test_imagenet_main_serial_native(tmp_path):
     assert "backend=native" in out and "step = 12" in out
 
 
-def test_gpu_jpeg_input_path_matches_the_host_path(tmp_path):
+@pytest.mark.parametrize("decoder", ["native", "torchvision"])
+def test_gpu_jpeg_input_path_matches_the_host_path(tmp_path, decoder):
     """TFRecord shards of synthetic JPEGs through both ImageNet input paths: PIL decode + numpy
     resize/crop on the host vs nvJPEG batch decode + drn_resize_crop_batch on the device.  Both
     draw the same crop decisions; the decoders may differ by a grey level or two."""
@@ -61,8 +62,11 @@ def test_gpu_jpeg_input_path_matches_the_host_path(tmp_path):
     from PIL import Image
     from distributed_resnet_tensorflow_b200.data import imagenet as im
     from distributed_resnet_tensorflow_b200.data.tfrecord import make_example, write_tfrecords
-    if not im.gpu_decode_available():
-        pytest.skip("torchvision GPU JPEG decode not available")
+    if decoder == "torchvision":
+        pytest.importorskip("torchvision")
+    else:
+        from distributed_resnet_tensorflow_b200.data import jpeg_native
+        assert jpeg_native.available(), "libdrn_b200.so was built without the nvJPEG binding"
     rng = np.random.default_rng(0)
     records = []
     for i in range(12):
@@ -79,7 +83,10 @@ def test_gpu_jpeg_input_path_matches_the_host_path(tmp_path):
     write_tfrecords(shard, records)
     for training in (False, True):
         host = list(im.ImageNetBatches(str(tmp_path), 4, training, 1, seed=3, files=[shard]))
-        dev = list(im.ImageNetBatchesGPU(str(tmp_path), 4, training, 1, seed=3, files=[shard], device="cuda:0"))
+        it = im.ImageNetBatchesGPU(str(tmp_path), 4, training, 1, seed=3, files=[shard], device="cuda:0",
+                                   decoder=decoder)
+        assert (it.native is not None) == (decoder == "native"), it.decoder_name
+        dev = list(it)
         assert len(host) == len(dev) == 3
         for (hi, hl, hc), (di, dl, dc) in zip(host, dev):
             assert di.is_cuda and di.dtype == torch.uint8 and tuple(di.shape) == hi.shape

@@ -158,3 +158,31 @@ def test_legacy_build_input_and_vgg_module(tmp_path):
     out = vgg_preprocessing.preprocess_image(img, 224, 224, is_training=False)
     assert out.shape == (224, 224, 3) and np.allclose(out, preprocess.vgg_preprocess(img, False))
     assert vgg_preprocessing.preprocess_image(img, 224, 224, True, rng=np.random.default_rng(1)).shape == (224, 224, 3)
+
+
+def test_multi_process_readers_deliver_every_example_once(tmp_path):
+    """--input_workers: reader processes over disjoint shard subsets (host JPEG path)."""
+    import io
+    from PIL import Image
+    from distributed_resnet_tensorflow_b200.data import imagenet as im
+    from distributed_resnet_tensorflow_b200.data.tfrecord import make_example, write_tfrecords
+    rng = np.random.default_rng(0)
+    files, label = [], 1
+    for s_ in range(2):
+        recs = []
+        for _ in range(6):
+            img = rng.integers(0, 255, (260, 300, 3), dtype=np.uint8)
+            buf = io.BytesIO()
+            Image.fromarray(img).save(buf, format="JPEG", quality=80)
+            recs.append(make_example({"image/encoded": [buf.getvalue()], "image/class/label": [label]}))
+            label += 1
+        f = str(tmp_path / ("validation-%05d-of-00128" % s_))
+        write_tfrecords(f, recs)
+        files.append(f)
+    mp = im.MultiProcessBatches(str(tmp_path), 3, False, 1, seed=0, workers=2, num_threads=2, files=files)
+    labels = []
+    for imgs, labs, crop in mp:
+        assert imgs.shape == (3, 224 * 224 * 3) and imgs.dtype == np.uint8 and crop.shape == (3, 3)
+        labels.extend(int(x) for x in labs)
+    mp.close()
+    assert sorted(labels) == list(range(1, 13))

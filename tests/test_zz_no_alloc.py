@@ -65,6 +65,43 @@ def test_static_scratch_variant_matches_on_two_consecutive_calls():
     assert (got2 - ref2).abs().max() <= 0.02 * ref2.abs().max() + 1e-3
 
 
+def test_static_scratch_variant_back_to_back_without_sync_and_without_allocating():
+    """Two different problems enqueued on ONE stream with no synchronisation in between (the second
+    overwrites the scratch the first has just read: stream order must be enough), and the amount of
+    free device memory is the same before and after warmed calls - the entry point allocates nothing."""
+    nl, lib = _lib()
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    probs = [_problem(8, 28, 128, 128, 3, 2, seed=21), _problem(4, 14, 256, 64, 3, 2, seed=22)]
+    prepared = []
+    for g, w, dy in probs:
+        wd = torch.empty(w.numel(), dtype=torch.bfloat16, device="cuda")
+        nl.check(lib.drn_weight_prep_dgrad(w.data_ptr(), wd.data_ptr(), g.K, g.R, g.S, g.C, st), "weight_prep")
+        d = g.desc()
+        need = lib.drn_conv_dgrad_scratch_bytes(ctypes.byref(d))
+        scratch = torch.empty(need, dtype=torch.uint8, device="cuda")
+        ref = torch.empty((g.N, g.H, g.W, g.C), dtype=torch.bfloat16, device="cuda")
+        nl.check(lib.drn_conv_dgrad(ctypes.byref(d), dy.data_ptr(), wd.data_ptr(), ref.data_ptr(), None, None, 0,
+                                    None, 0, scratch.data_ptr(), need, st), "drn_conv_dgrad")
+        got = torch.full_like(ref, float("nan"))
+        prepared.append((d, dy, wd, ref, got))
+    # warm call (resolves the array's address on this device), then measure free memory
+    d, dy, wd, ref, got = prepared[0]
+    nl.check(lib.drn_conv_dgrad_static(ctypes.byref(d), dy.data_ptr(), wd.data_ptr(), got.data_ptr(), None, None,
+                                       0, None, 0, st), "drn_conv_dgrad_static")
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info()
+    for d, dy, wd, ref, got in prepared:          # no synchronisation between the two calls
+        nl.check(lib.drn_conv_dgrad_static(ctypes.byref(d), dy.data_ptr(), wd.data_ptr(), got.data_ptr(), None,
+                                           None, 0, None, 0, st), "drn_conv_dgrad_static")
+    torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info()
+    assert free_after == free_before, (free_before, free_after)
+    for d, dy, wd, ref, got in prepared:
+        r, g_ = ref.float(), got.float()
+        assert torch.isfinite(g_).all()
+        assert (g_ - r).abs().max() <= 0.02 * r.abs().max() + 1e-3
+
+
 def test_static_scratch_variant_refuses_oversized_problems():
     nl, lib = _lib()
     g, w, dy = _problem(1, 8, 64, 64, 3, 2, seed=13)
