@@ -53,6 +53,10 @@ struct ConvParams {
   int stats_ld;    // leading dimension of stats rows
   float* stats;    // [2][stats_ld]
   const float2* bn_scale_shift;  // [Cout] (scale, shift) of the BN whose backward mask is applied
+  const float4* bn_coef;         // [Cout] (A, B, C, -) of dy = A*dm + B*y + C (BNBWD_APPLY)
+  int no_store;                  // statistics only: the tile is reduced but not written (BNBWD / BNBWD_ADD)
+  int side2_first;               // BNBWD_APPLY: side2 is added BEFORE the mask (gradient of a second branch)
+                                 //              instead of after the BatchNorm-backward formula (shortcut gradient)
   // PRE variant: the A operand is relu(x * scale + shift) of the RAW tensor x (BatchNorm + ReLU of
   // the consuming layer applied in shared memory between the TMA load and the MMA)
   const float2* pre_ss;  // [C] (scale, shift)
@@ -64,6 +68,14 @@ struct ConvParams {
   PullArgs pull;         // pull.shadows.p[0] == nullptr: weights are already local
 };
 constexpr int kPreThreads = 128;    // warps 12-15 of the PRE variant
+
+// second side input / coefficient table of the two-side epilogue modes (thread-local request set by
+// drn_conv_igemm_epi2 around the ordinary launcher)
+struct Epi2 {
+  const void* side2;
+  const void* coef;
+  int side2_first;
+};
 
 constexpr int kMaxRes = 8;          // side-input ring depth per epilogue group (upper bound)
 constexpr int kSmemBudget = 226 * 1024;
@@ -80,7 +92,7 @@ struct Cfg {
   static constexpr int kRowBytes = kCW * 2;            // bytes per staged row (= swizzle span)
   static constexpr int kChunkBytes = kBM * kRowBytes;  // <= 8 KB
   static constexpr int kOutBytes = 2 * kEpiBufs * kChunkBytes;   // 2 groups x out[kEpiBufs]
-  static constexpr int kAuxBytes = 4096 + 2048 + 1024;  // 2 x scale/shift cache, 2 x stats scratch, barriers
+  static constexpr int kAuxBytes = 4096 + 2048 + 1024 + 8192;  // 2 x scale/shift cache, 2 x stats scratch, barriers, 2 x coefficient cache
   static constexpr int kTmemColsRaw = 2 * BN;
   static constexpr int kTmemCols = kTmemColsRaw <= 32    ? 32
                                    : kTmemColsRaw <= 64  ? 64
@@ -104,7 +116,7 @@ template <int KC, int BN, bool PRE = false, bool TWO = false, int EPI = -1>
 __global__ void __launch_bounds__(PRE ? kNumThreads + kPreThreads : kNumThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapB,
                   const __grid_constant__ CUtensorMap tmapC, const __grid_constant__ CUtensorMap tmapR,
-                  const ConvParams p) {
+                  const __grid_constant__ CUtensorMap tmapR2, const ConvParams p) {
   using C_ = Cfg<KC, BN, TWO>;
   static_assert(!(PRE && TWO), "the BatchNorm prologue has no CTA-pair variant");
   const int kStages = p.n_stages;
@@ -127,7 +139,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
   const uint32_t sStages = smem_base;
   const uint32_t sOut = sStages + kStages * C_::kStageBytes;
   const uint32_t sRes = sOut + C_::kOutBytes;
-  const uint32_t sAux = sRes + 2 * p.n_res * C_::kChunkBytes;
+  const bool two_side = mode == DRN_EPI_BNBWD_ADD || mode == DRN_EPI_BNBWD_APPLY;
+  const uint32_t sRes2 = sRes + 2 * p.n_res * C_::kChunkBytes;      // second side-input rings (two_side)
+  const uint32_t sAux = sRes2 + (two_side ? 2 * p.n_res * C_::kChunkBytes : 0);
   float2* sScaleShift = reinterpret_cast<float2*>(smem_gen + (sAux - smem_base));  // 2 x 256 entries
   const uint32_t sBar = sAux + 4096 + 2048;
   // barrier map (8 bytes each)
@@ -136,6 +150,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
   auto tfull_bar = [&](int b) { return sBar + 8u * (2 * kMaxStages + b); };
   auto tempty_bar = [&](int b) { return sBar + 8u * (2 * kMaxStages + 2 + b); };
   auto res_bar = [&](int b) { return sBar + 8u * (2 * kMaxStages + 4 + b); };  // b in [0, 2*kMaxRes)
+  float4* sCoef = reinterpret_cast<float4*>(smem_gen + (sBar + 1024 - smem_base));   // 2 x 256 entries
   const uint32_t sTmemPtr = sBar + 8u * (2 * kMaxStages + 4 + 2 * kMaxRes);
   auto ready_bar = [&](int s) { return sBar + 8u * (2 * kMaxStages + 4 + 2 * kMaxRes + 1 + s); };  // PRE
   volatile uint32_t* tmem_ptr_gen =
@@ -160,6 +175,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     tma_prefetch_desc(&tmapB);
     tma_prefetch_desc(&tmapC);
     if (mode != DRN_EPI_PLAIN) tma_prefetch_desc(&tmapR);
+    if (two_side) tma_prefetch_desc(&tmapR2);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -403,8 +419,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     const uint32_t bar_id = 1 + grp;
     const uint32_t out_base = sOut + grp * kEpiBufs * C_::kChunkBytes;
     const uint32_t res_base = sRes + grp * p.n_res * C_::kChunkBytes;
+    const uint32_t res2_base = sRes2 + grp * p.n_res * C_::kChunkBytes;
     const uint32_t n_res = p.n_res;
     float2* my_ss = sScaleShift + grp * 256;
+    float4* my_coef = sCoef + grp * 256;
     float* my_red = reinterpret_cast<float*>(sScaleShift + 512) + grp * 256;  // [2][kHalf*kCW]
     constexpr int kHalf = C_::kChunks >= 2 ? C_::kChunks / 2 : 1;  // chunks per tile per group
     // swizzled byte offsets of my row's 16-byte pieces inside a staging buffer (chunk independent)
@@ -470,9 +488,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     uint32_t pf_slot = 0;
     auto issue_next_res_load = [&]() {
       if (pf_tile < t_end) {
-        mbar_arrive_expect_tx(res_bar(grp * kMaxRes + pf_slot), C_::kChunkBytes);
+        mbar_arrive_expect_tx(res_bar(grp * kMaxRes + pf_slot), (two_side ? 2 : 1) * C_::kChunkBytes);
         tma_load_2d(res_base + pf_slot * C_::kChunkBytes, &tmapR, res_bar(grp * kMaxRes + pf_slot),
                     pf_n * BN + pf_chunk * kCW, row_tile(pf_m) * kBM);
+        if (two_side)   // both side tiles of a chunk land on the same barrier
+          tma_load_2d(res2_base + pf_slot * C_::kChunkBytes, &tmapR2, res_bar(grp * kMaxRes + pf_slot),
+                      pf_n * BN + pf_chunk * kCW, row_tile(pf_m) * kBM);
       }
       if (++pf_slot == n_res) pf_slot = 0;
       pf_chunk += 2;                       // the other group takes the chunks in between
@@ -489,7 +510,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     uint32_t mine = 0;  // chunks processed by this group so far
     uint32_t rb = 0, rb_phase = 0;  // ring slot / phase of the chunk being processed (= mine % n_res, ...)
     uint32_t ob = 0;                // staging buffer of the chunk being processed (= mine % kEpiBufs)
-    const bool late_refill = want_stats && mode == DRN_EPI_BNBWD;
+    const bool mask_mode = mode == DRN_EPI_BNBWD || two_side;   // the side tile is the BatchNorm input
+    const bool late_refill = want_stats && (mode == DRN_EPI_BNBWD || mode == DRN_EPI_BNBWD_ADD);
     if (has_res && leader) {
       // fill the ring: chunks 0 .. n_res-2 (chunk i + n_res - 1 is requested when chunk i starts)
       for (uint32_t i = 0; i + 1 < n_res; ++i) issue_next_res_load();
@@ -506,11 +528,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
         if (n_tile != cur_n_tile) {
           flush_stats(cur_n_tile);
           cur_n_tile = n_tile;
-          if (mode == DRN_EPI_BNBWD) {
+          if (mask_mode) {
             named_bar_sync(bar_id, kEpiThreads);
             for (int i = et; i < BN; i += kEpiThreads) {
               const int col = n_tile * BN + i;
               my_ss[i] = col < p.n_valid ? p.bn_scale_shift[col] : make_float2(0.f, 0.f);
+              if (mode == DRN_EPI_BNBWD_APPLY)
+                my_coef[i] = col < p.n_valid ? p.bn_coef[col] : make_float4(0.f, 0.f, 0.f, 0.f);
             }
             named_bar_sync(bar_id, kEpiThreads);
           }
@@ -523,6 +547,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           const int j = C_::kChunks >= 2 ? 2 * a + grp : 0;
           const uint32_t out_buf = out_base + ob * C_::kChunkBytes;
           const uint32_t res_buf = res_base + rb * C_::kChunkBytes;
+          const uint32_t res2_buf = res2_base + rb * C_::kChunkBytes;
           // request the side input n_res-1 chunks ahead; it lands in the ring slot of the previous
           // chunk, whose main-pass readers all passed that chunk's barrier.  When the statistics read
           // the side tile too (BNBWD), they may still be running: refill after THIS chunk's barrier.
@@ -573,7 +598,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                   v[c16 * 8 + e * 2 + 1] += bf16hi(rr[e]);
                 }
               }
-            } else {  // DRN_EPI_BNBWD: keep the gradient where relu(bn(y)) was active
+            } else if (mode == DRN_EPI_BNBWD) {  // keep the gradient where relu(bn(y)) was active
 #pragma unroll
               for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
                 const uint4 rv = ld_shared_v4(res_buf + row_off[c16]);
@@ -585,6 +610,39 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
                   const float2 ss1 = my_ss[j * kCW + c0 + 1];
                   v[c0] = (fmaf(bf16lo(rr[e]), ss0.x, ss0.y) > 0.f) ? v[c0] : 0.f;
                   v[c0 + 1] = (fmaf(bf16hi(rr[e]), ss1.x, ss1.y) > 0.f) ? v[c0 + 1] : 0.f;
+                }
+              }
+            } else {
+              // two side tiles: y (the BatchNorm input, mask source) and a second tensor that is either
+              // added before the mask (gradient arriving through a second branch: BNBWD_ADD, or
+              // BNBWD_APPLY with side2_first) or after the BatchNorm-backward formula (the identity
+              // shortcut's gradient).  BNBWD_APPLY finishes the BatchNorm backward right here:
+              //   out = A * (acc * [relu(bn(y)) active]) + B * y + C  (+ side2)
+              const bool apply = mode == DRN_EPI_BNBWD_APPLY;
+              const bool add_first = !apply || p.side2_first != 0;
+#pragma unroll
+              for (int c16 = 0; c16 < kRowBytes / 16; ++c16) {
+                const uint4 rv = ld_shared_v4(res_buf + row_off[c16]);
+                const uint4 sv = ld_shared_v4(res2_buf + row_off[c16]);
+                const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w};
+                const uint32_t s2[4] = {sv.x, sv.y, sv.z, sv.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+#pragma unroll
+                  for (int hh = 0; hh < 2; ++hh) {
+                    const int c0 = c16 * 8 + e * 2 + hh;
+                    const float yv = hh ? bf16hi(rr[e]) : bf16lo(rr[e]);
+                    const float tv = hh ? bf16hi(s2[e]) : bf16lo(s2[e]);
+                    const float2 ss0 = my_ss[j * kCW + c0];
+                    float g = add_first ? v[c0] + tv : v[c0];
+                    g = (fmaf(yv, ss0.x, ss0.y) > 0.f) ? g : 0.f;
+                    if (apply) {
+                      const float4 cf = my_coef[j * kCW + c0];
+                      g = fmaf(cf.x, g, fmaf(cf.y, yv, cf.z));
+                      if (!add_first) g += tv;
+                    }
+                    v[c0] = g;
+                  }
                 }
               }
             }
@@ -607,14 +665,16 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           if (leader) tma_store_wait_read<1>();
           named_bar_sync(bar_id, kEpiThreads);
           if (leader) {
-            tma_store_2d(&tmapC, out_buf, n_tile * BN + j * kCW, m_tile * kBM);
-            tma_store_commit();
+            if (!p.no_store) {
+              tma_store_2d(&tmapC, out_buf, n_tile * BN + j * kCW, m_tile * kBM);
+              tma_store_commit();
+            }
             if (has_res && late_refill) issue_next_res_load();
           }
 
           // ---- per-channel statistics of what was just stored (bf16-rounded values)
           if (want_stats) {
-            if (mode == DRN_EPI_BNBWD) {
+            if (mode == DRN_EPI_BNBWD || mode == DRN_EPI_BNBWD_ADD) {
 #pragma unroll
               for (int i = 0; i < kNcg; ++i) {
                 const uint4 ov = ld_shared_v4(out_buf + st_off[i]);
@@ -678,7 +738,7 @@ inline int env_int(const char* name, int dflt) {
 
 template <int KC, int BN, bool PRE, bool TWO, int EPI>
 int launch_instance(int grid, int threads, int smem_bytes, cudaStream_t stream, const CUtensorMap& tA,
-                    const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tR, const ConvParams& p) {
+                    const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tR, const CUtensorMap& tR2, const ConvParams& p) {
   static PerDeviceOnce attr_set;
   if (attr_set.need()) {
     DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<KC, BN, PRE, TWO, EPI>,
@@ -687,10 +747,10 @@ int launch_instance(int grid, int threads, int smem_bytes, cudaStream_t stream, 
   }
   if constexpr (TWO) {
     DRN_CHECK_CUDA(launch_cluster2(conv_igemm_kernel<KC, BN, PRE, TWO, EPI>, dim3(grid), dim3(threads),
-                                   smem_bytes, stream, tA, tB, tC, tR, p));
+                                   smem_bytes, stream, tA, tB, tC, tR, tR2, p));
   } else {
     DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN, PRE, TWO, EPI>, dim3(grid), dim3(threads),
-                                   smem_bytes, stream, tA, tB, tC, tR, p));
+                                   smem_bytes, stream, tA, tB, tC, tR, tR2, p));
   }
   return 0;
 }
@@ -699,19 +759,19 @@ int launch_instance(int grid, int threads, int smem_bytes, cudaStream_t stream, 
 // k-block kernels (ImageNet-sized layers); everything else runs the generic one.
 template <int KC, int BN, bool PRE, bool TWO>
 int launch_variant(int epi, int grid, int threads, int smem_bytes, cudaStream_t stream, const CUtensorMap& tA,
-                   const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tR, const ConvParams& p) {
+                   const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tR, const CUtensorMap& tR2, const ConvParams& p) {
   if constexpr (KC == 64 && BN >= 64) {
     switch (epi) {
-      case 0: return launch_instance<KC, BN, PRE, TWO, 0>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
-      case 1: return launch_instance<KC, BN, PRE, TWO, 1>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
+      case 0: return launch_instance<KC, BN, PRE, TWO, 0>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
+      case 1: return launch_instance<KC, BN, PRE, TWO, 1>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
       default: break;
     }
     if constexpr (!PRE) {
-      if (epi == 3) return launch_instance<KC, BN, PRE, TWO, 3>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
-      if (epi == 5) return launch_instance<KC, BN, PRE, TWO, 5>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
+      if (epi == 3) return launch_instance<KC, BN, PRE, TWO, 3>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
+      if (epi == 5) return launch_instance<KC, BN, PRE, TWO, 5>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
     }
   }
-  return launch_instance<KC, BN, PRE, TWO, -1>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, p);
+  return launch_instance<KC, BN, PRE, TWO, -1>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
 }
 
 template <int KC, int BN, bool TWO = false>
@@ -748,18 +808,31 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   // the BN-backward epilogue refills a ring slot half a chunk later (after the chunk's barrier) and
   // streams a wide side tensor: it wants the deeper ring up to longer reductions (measured)
   if (mode == DRN_EPI_BNBWD && (k_iters_total <= 4 || (k_iters_total <= 8 && d.K >= 4 * d.C))) n_res_dflt = 4;
+  const bool two_side = mode == DRN_EPI_BNBWD_ADD || mode == DRN_EPI_BNBWD_APPLY;
+  const Epi2* e2 = static_cast<const Epi2*>(current_epi2());
+  if (two_side) {
+    DRN_REQUIRE(e2 != nullptr && e2->side2 != nullptr, "conv_igemm: mode %d needs a second side input", mode);
+    DRN_REQUIRE(mode != DRN_EPI_BNBWD_APPLY || e2->coef != nullptr, "conv_igemm: BNBWD_APPLY needs the coefficient table");
+    n_res_dflt = env_int("DRN_NRES2", 2);          // two rings per group: keep them short
+  }
   p.n_res = mode == DRN_EPI_PLAIN ? 0 : env_int("DRN_NRES", n_res_dflt);
-  p.n_stages = C_::stages_for(p.n_res);
+  const int rings = p.n_res * (two_side ? 2 : 1);   // side-tile slots per epilogue group
+  p.n_stages = C_::stages_for(rings);
   if (int cap = env_int("DRN_STAGES", 0)) p.n_stages = p.n_stages < cap ? p.n_stages : cap;   // experiments
   if (p.n_stages < 2) return fail("conv_igemm: shared memory plan does not fit (KC=%d BN=%d)", KC, BN);
-  const int smem_bytes = C_::smem_for(p.n_res, p.n_stages);
+  const int smem_bytes = C_::smem_for(rings, p.n_stages);
+  p.no_store = y == nullptr ? 1 : 0;
+  DRN_REQUIRE(!p.no_store || (stats != nullptr && (mode == DRN_EPI_BNBWD || mode == DRN_EPI_BNBWD_ADD)),
+              "conv_igemm: y may only be NULL for a statistics-only BNBWD / BNBWD_ADD launch");
+  p.bn_coef = e2 != nullptr ? reinterpret_cast<const float4*>(e2->coef) : nullptr;
+  p.side2_first = e2 != nullptr ? e2->side2_first : 0;
   p.want_stats = stats != nullptr;
   p.n_valid = d.K;
   p.stats_ld = stats_ld;
   p.stats = stats;
   p.bn_scale_shift = reinterpret_cast<const float2*>(bn_scale_shift);
 
-  CUtensorMap tA, tB, tC, tR;
+  CUtensorMap tA, tB, tC, tR, tR2;
   if (int e = tmap_im2col_nhwc(&tA, x, d.N, d.H, d.W, d.C, -d.pad_lo, -pad_w_lo,
                                d.pad_hi - (d.R - 1), pad_w_hi - (d.S - 1), d.stride, d.stride, KC,
                                kBM, KC * 2, view ? vstr : nullptr))
@@ -767,12 +840,20 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   if (int e = tmap_tiled_2d(&tB, w, 2, d.K, (uint64_t)d.R * d.S * d.C, (uint64_t)d.R * d.S * d.C,
                             C_::kBRows, KC, KC * 2))
     return e;
-  if (int e = tmap_tiled_2d(&tC, y, 2, (uint64_t)M, d.K, d.K, kBM, C_::kCW, C_::kRowBytes)) return e;
+  if (y != nullptr)
+    if (int e = tmap_tiled_2d(&tC, y, 2, (uint64_t)M, d.K, d.K, kBM, C_::kCW, C_::kRowBytes)) return e;
   if (mode != DRN_EPI_PLAIN) {
     if (int e = tmap_tiled_2d(&tR, side, 2, (uint64_t)M, d.K, d.K, kBM, C_::kCW, C_::kRowBytes))
       return e;
+    if (y == nullptr) tC = tR;
   } else {
     tR = tC;
+  }
+  if (two_side) {
+    if (int e = tmap_tiled_2d(&tR2, e2->side2, 2, (uint64_t)M, d.K, d.K, kBM, C_::kCW, C_::kRowBytes))
+      return e;
+  } else {
+    tR2 = tR;
   }
 
   int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
@@ -786,19 +867,19 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
     DRN_REQUIRE(p.pre_ss == nullptr, "conv_igemm: no CTA-pair variant of the BatchNorm prologue");
     const int pairs = num_sms() / 2;
     grid = 2 * (p.total_tiles < pairs ? p.total_tiles : pairs);
-    return launch_variant<KC, BN, false, true>(epi, grid, kNumThreads, smem_bytes, stream, tA, tB, tC, tR, p);
+    return launch_variant<KC, BN, false, true>(epi, grid, kNumThreads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
   }
   if (p.pre_ss != nullptr) {
     if constexpr (KC == 64 && (BN == 64 || BN == 128)) {
       DRN_REQUIRE(d.R == 1 && d.S == 1 && d.pad_lo == 0 && d.pad_hi == 0 && view == nullptr,
                   "conv_igemm: the BatchNorm prologue supports 1x1 convolutions only");
       return launch_variant<KC, BN, true, false>(epi, grid, kNumThreads + kPreThreads, smem_bytes, stream, tA,
-                                                 tB, tC, tR, p);
+                                                 tB, tC, tR, tR2, p);
     } else {
       return fail("conv_igemm: the BatchNorm prologue needs C %% 64 == 0 and an N tile of 64 or 128 (got KC=%d BN=%d)", KC, BN);
     }
   }
-  return launch_variant<KC, BN, false, false>(epi, grid, kNumThreads, smem_bytes, stream, tA, tB, tC, tR, p);
+  return launch_variant<KC, BN, false, false>(epi, grid, kNumThreads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
 }
 
 template <int KC>
@@ -833,8 +914,10 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
   DRN_REQUIRE(d.K % 16 == 0, "conv_igemm: K must be a multiple of 16 (got %d)", d.K);
   DRN_REQUIRE(mode == DRN_EPI_PLAIN || side != nullptr, "conv_igemm: mode %d needs a side input",
               mode);
-  DRN_REQUIRE(mode != DRN_EPI_BNBWD || bn_scale_shift != nullptr,
-              "conv_igemm: BNBWD mode needs bn_scale_shift");
+  DRN_REQUIRE(mode >= DRN_EPI_PLAIN && mode <= DRN_EPI_BNBWD_APPLY, "conv_igemm: unknown epilogue mode %d", mode);
+  DRN_REQUIRE(mode < DRN_EPI_BNBWD || bn_scale_shift != nullptr,
+              "conv_igemm: the BNBWD modes need bn_scale_shift");
+  DRN_REQUIRE(mode != DRN_EPI_BNBWD_APPLY || stats == nullptr, "conv_igemm: BNBWD_APPLY takes no statistics");
   DRN_REQUIRE(stats == nullptr || stats_ld >= d.K, "conv_igemm: stats_ld < K");
   int bn = force_bn;
   if (bn == 0) {
@@ -1028,5 +1111,21 @@ extern "C" int drn_conv_igemm_ex(const drn_conv_desc* desc, const drn_conv_view*
   current_pre() = nullptr;
   current_view() = nullptr;
   current_pull() = nullptr;
+  return rc;
+}
+
+// Two-side epilogues (BatchNorm backward finished inside the data-gradient kernel):
+//   DRN_EPI_BNBWD_ADD    y = (conv + side2) * [relu(bn(side)) active]; stats += (sum y, sum y*side)
+//   DRN_EPI_BNBWD_APPLY  y = A*(conv [+ side2 if side2_first]) * [active] + B*side + C [+ side2 otherwise]
+// y may be NULL for a statistics-only launch of BNBWD / BNBWD_ADD (first of the two passes that
+// replace "masked gradient to memory, then an element-wise BatchNorm-backward pass").
+extern "C" int drn_conv_igemm_epi2(const drn_conv_desc* desc, const void* x, const void* w, void* y,
+                                   const void* side, const void* side2, float* stats, int stats_ld,
+                                   const void* bn_scale_shift, const void* bn_coef, int side2_first,
+                                   int mode, int force_bn, void* stream) {
+  drn::Epi2 e2{side2, bn_coef, side2_first};
+  drn::current_epi2() = &e2;
+  const int rc = drn_conv_igemm(desc, x, w, y, side, stats, stats_ld, bn_scale_shift, mode, force_bn, stream);
+  drn::current_epi2() = nullptr;
   return rc;
 }

@@ -41,6 +41,11 @@ const void*& current_pull() {
   return v;
 }
 
+const void*& current_epi2() {
+  static thread_local const void* v = nullptr;
+  return v;
+}
+
 int pdl_mask() {
   static const int m = []() {
     const char* e = getenv("DRN_PDL");

@@ -119,5 +119,8 @@ const void*& current_pre();
 // Optional "fetch the filter bank from the parameter-server shards first" request of
 // drn_conv_igemm_ex (thread-local, set around the ordinary launcher); points at a drn::PullArgs.
 const void*& current_pull();
+// Optional second side input of the two-side epilogue modes (drn_conv_igemm_epi2); points at a
+// conv_igemm.cu Epi2.
+const void*& current_epi2();
 
 }  // namespace drn

@@ -36,7 +36,7 @@ class ConvView(ctypes.Structure):
                 ("stride_n", ctypes.c_longlong), ("pad_w_lo", ctypes.c_int), ("pad_w_hi", ctypes.c_int)]
 
 
-EPI_PLAIN, EPI_RESADD, EPI_BNBWD = 0, 1, 2
+EPI_PLAIN, EPI_RESADD, EPI_BNBWD, EPI_BNBWD_ADD, EPI_BNBWD_APPLY = 0, 1, 2, 3, 4
 
 _lib = None
 
@@ -54,6 +54,7 @@ _SIGNATURES = {
     "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
     "drn_conv_igemm_ex": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, ctypes.POINTER(PullDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
+    "drn_conv_igemm_epi2": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp]),
     "drn_conv_igemm_view": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_resize_crop_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "drn_weight_prep_dgrad_s2": (_i, [_vp, _vp, _i, _i, _vp]),

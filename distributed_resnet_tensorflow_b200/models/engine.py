@@ -28,7 +28,8 @@ import numpy as np
 import torch
 
 from .._native import lib as _nl
-from .._native.lib import ConvDesc, ConvView, EPI_BNBWD, EPI_PLAIN, EPI_RESADD, PullDesc
+from .._native.lib import (ConvDesc, ConvView, EPI_BNBWD, EPI_BNBWD_ADD, EPI_BNBWD_APPLY, EPI_PLAIN, EPI_RESADD,
+                           PullDesc)
 from ..ops.conv import ConvGeom
 from .spec import BlockSpec, BNSpec, ConvSpec, NetSpec
 
@@ -52,6 +53,26 @@ def _fuse_bn0(blk: BlockSpec) -> bool:
     if blk.cin not in (256, 512, 1024) or blk.cin > int(os.environ.get("DRN_FUSE_BN0_MAXC", "512")):
         return False
     return blk.proj is None or blk.cin == 256
+
+
+def _fuse_bnbwd(blk: BlockSpec) -> bool:
+    """BatchNorm backward of the block's FIRST BatchNorm finished inside the data-gradient kernel of
+    its 1x1 consumer (two passes of the cheap convolution: statistics, then apply) instead of writing
+    the masked gradient and running an element-wise pass over the wide tensor.  It moves 2W - N fewer
+    bytes per block (W/N = wide/narrow activation), but measured on B200 it does NOT pay: the
+    mask+statistics epilogue is bound by its instruction count, not by HBM (a statistics-only pass
+    over 256 MB takes 97 us where the store-ing one takes 107 us), so the two passes cost what the
+    fused-epilogue + element-wise pair costs (bench/prof_epi2.py: 233-264 us vs 243 us at 56x56,
+    140 vs 142 us at 28x28, worse below) and the step time is unchanged (8.80 ms either way).
+    Therefore OFF by default; DRN_FUSE_BNBWD=1 enables it for feature maps >= DRN_FUSE_BNBWD_MINHW."""
+    c0 = blk.convs[0]
+    if os.environ.get("DRN_FUSE_BNBWD", "0") != "1" or c0.ksize != 1 or c0.stride != 1 or len(blk.convs) != 3:
+        return False
+    if blk.hin < int(os.environ.get("DRN_FUSE_BNBWD_MINHW", "14")):
+        return False
+    return blk.proj is None or blk.proj.stride == 1
+
+
 BN_EPS = 1e-5
 VGG_MEANS = (123.68 / 255.0, 116.78 / 255.0, 103.94 / 255.0)  # vgg_preprocessing.py:37-39 (in [0,1] units)
 
@@ -374,6 +395,7 @@ class NativeResNet:
         d = {"spec": blk}
         d["bn0"] = _BN(blk.bns[0], self)
         d["fuse"] = _fuse_bn0(blk)
+        d["fuse_bwd"] = _fuse_bnbwd(blk)
         d["a0"] = None if d["fuse"] else self._act(B, blk.hin, blk.hin, blk.cin)
         sizes = [B * blk.hin * blk.hin * blk.cin]
         if blk.proj is not None:
@@ -763,6 +785,16 @@ class NativeResNet:
         if range_hook is not None:
             range_hook(marks[0], marks[1], True)
 
+    def _dgrad_epi2(self, conv: _Conv, dy, out, side, side2, bn: _BN, mode, stats: bool, first: bool = False):
+        """Stride-1 data gradient of ``conv`` with one of the two-side epilogues (out=None: statistics only)."""
+        _nl.call("drn_conv_igemm_epi2", ctypes.byref(conv.dg_desc), _p(dy), _p(conv.wd), _p(out), _p(side), _p(side2),
+                 _p(bn.bstats) if stats else 0, bn.bstats.stride(0) if stats else 0, _p(bn.ss),
+                 _p(bn.coef) if mode == EPI_BNBWD_APPLY else 0, 1 if first else 0, mode, 0, self._st())
+
+    def _bn_bwd_coef(self, bn: _BN, count: int):
+        _nl.call("drn_bn_bwd_finalize", _p(bn.bstats), bn.bstats.stride(0), count, _p(bn.gamma), _p(bn.mi),
+                 _p(bn.dgamma), _p(bn.dbeta), _p(bn.coef), bn.C, self._st())
+
     def _bn_bwd(self, bn: _BN, dm, y, addend, out):
         st = self._st()
         count = y.numel() // bn.C
@@ -807,6 +839,20 @@ class NativeResNet:
         if "proj" in b:
             pj = b["proj"]
             self._wgrad(pj, a0, g, g_i, pre=pre0)
+            if b["fuse_bwd"]:
+                # t = data gradient through the projection (computed once); the cheap 1x1 main-path
+                # gradient is recomputed: pass 1 reduces (t + dgrad) under the mask, pass 2 applies
+                t_i, t = self._get(x)
+                self._conv(pj.dg_desc, g, pj.wd, t)
+                self._put(g_i)
+                self._dgrad_epi2(c0, dy, None, x, t, bn0, EPI_BNBWD_ADD, stats=True)
+                self._bn_bwd_coef(bn0, x.numel() // C)
+                gin_i, gin = self._get(x)
+                self._dgrad_epi2(c0, dy, gin, x, t, bn0, EPI_BNBWD_APPLY, stats=False, first=True)
+                if dy_i != g_i:
+                    self._put(dy_i)
+                self._put(t_i)
+                return gin_i, gin
             da_i, da = self._get(x)
             self._dgrad(c0, dy, da)
             if dy_i != g_i:
@@ -830,6 +876,15 @@ class NativeResNet:
             gin_i, gin = self._get(x)
             self._bn_bwd(bn0, dm, x, None, gin)
             self._put(dm_i)
+            return gin_i, gin
+        if b["fuse_bwd"]:
+            self._dgrad_epi2(c0, dy, None, x, None, bn0, EPI_BNBWD, stats=True)
+            self._bn_bwd_coef(bn0, x.numel() // C)
+            gin_i, gin = self._get(x)
+            self._dgrad_epi2(c0, dy, gin, x, g, bn0, EPI_BNBWD_APPLY, stats=False)
+            if dy_i != g_i:
+                self._put(dy_i)
+            self._put(g_i)
             return gin_i, gin
         dm_i, dm = self._get(x)
         self._dgrad(c0, dy, dm, side=x, stats=bn0.bstats, ss=bn0.ss, mode=EPI_BNBWD)

@@ -118,3 +118,17 @@ def conv_dgrad(dy, w_dgrad, g: ConvGeom, out=None, side=None, stats=None, bn_sca
              stats_ld, _ptr(bn_scale_shift), mode, _ptr(scratch), scratch.numel() * 2 if scratch is not None else 0,
              _stream())
     return out
+
+
+def conv_fprop_epi2(x, w, g: ConvGeom, side, side2, out=None, stats=None, bn_scale_shift=None, bn_coef=None,
+                    side2_first: bool = False, mode: int = _nl.EPI_BNBWD_ADD, store: bool = True, force_bn: int = 0):
+    """Two-side epilogues of the implicit-GEMM kernel (drn_conv_igemm_epi2): BNBWD_ADD / BNBWD_APPLY, or a
+    statistics-only BNBWD / BNBWD_ADD pass with ``store=False`` (returns None)."""
+    if store and out is None:
+        out = torch.empty((g.N, g.P, g.Q, g.K), dtype=torch.bfloat16, device=x.device)
+    stats_ld = stats.stride(0) if stats is not None else 0
+    d = g.desc()
+    _nl.call("drn_conv_igemm_epi2", ctypes.byref(d), _ptr(x), _ptr(w), _ptr(out) if store else _ptr(None), _ptr(side),
+             _ptr(side2), _ptr(stats), stats_ld, _ptr(bn_scale_shift), _ptr(bn_coef), 1 if side2_first else 0, mode,
+             force_bn, _stream())
+    return out if store else None

@@ -38,7 +38,7 @@ from .._native import lib as _nl
 from .symm import SymmetricBuffer
 
 CH_ALLREDUCE, CH_PS, CH_BCAST, CH_BARRIER = 0, 1, 2, 3
-ONESHOT_MAX_BYTES = 4 << 20
+ONESHOT_MAX_BYTES = 256 << 10   # measured on 8 B200 (profiles/bench_8gpu_r2.jsonl): at 3 MB the one-shot kernel loses to two-shot (1.145 vs 1.116 ms/step on CIFAR)
 ALGOS = ("auto", "oneshot", "twoshot", "nccl", "none", "p2p", "oneshot_p2p", "twoshot_p2p", "multicast", "nvls")
 
 

@@ -46,8 +46,13 @@ typedef struct {
 enum {
   DRN_EPI_PLAIN = 0,  /* y = conv(x, w)                                                        */
   DRN_EPI_RESADD = 1, /* y = conv(x, w) + side                 (shortcut add, K10)             */
-  DRN_EPI_BNBWD = 2   /* y = conv(x, w) * [side*scale+shift > 0]   (ReLU+BN backward mask, K6/K9);
+  DRN_EPI_BNBWD = 2,  /* y = conv(x, w) * [side*scale+shift > 0]   (ReLU+BN backward mask, K6/K9);
                          stats then receive sum(y) and sum(y*side) per channel                  */
+  /* two side inputs (drn_conv_igemm_epi2): */
+  DRN_EPI_BNBWD_ADD = 3,   /* y = (conv + side2) * [side*scale+shift > 0]; stats as in BNBWD      */
+  DRN_EPI_BNBWD_APPLY = 4  /* y = A*(conv [+ side2]) * [side*scale+shift > 0] + B*side + C [+ side2]:
+                              the whole BatchNorm+ReLU backward of the layer in front (K6), with the
+                              coefficients of drn_bn_bwd_finalize                                */
 };
 
 /* Implicit-GEMM convolution on tcgen05/TMEM with im2col TMA.
@@ -61,6 +66,16 @@ enum {
 int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const void* w, void* y,
                    const void* side, float* stats, int stats_ld, const void* bn_scale_shift,
                    int mode, int force_bn, void* stream);
+
+/* Epilogues with a second side tensor (same shape as y).  mode = DRN_EPI_BNBWD_ADD or _APPLY
+ * (side2_first: _APPLY adds side2 before the mask - a second gradient branch - instead of after the
+ * BatchNorm formula - the identity shortcut's gradient), or DRN_EPI_BNBWD / _ADD with y = NULL for a
+ * statistics-only pass.  bn_coef = float4[K] from drn_bn_bwd_finalize.  Replaces "write the masked
+ * gradient, then run drn_bn_bwd_apply over it" by recomputing the (cheap, 1x1) convolution. */
+int drn_conv_igemm_epi2(const drn_conv_desc* desc, const void* x, const void* w, void* y,
+                        const void* side, const void* side2, float* stats, int stats_ld,
+                        const void* bn_scale_shift, const void* bn_coef, int side2_first, int mode,
+                        int force_bn, void* stream);
 
 /* The same two kernels over a strided (possibly overlapping) view of x: element strides between
  * pixels along W, rows and images, and zero padding along W given separately from desc->pad_*
