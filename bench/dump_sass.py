@@ -1,7 +1,7 @@
 """Regenerates profiles/sass/: `cuobjdump -sass` of libdrn_b200.so split per kernel, one file per
 kernel (the largest instantiation of each template family is kept in full, the others are counted),
 and SUMMARY.md with the mnemonic counts that identify the Blackwell paths
-(UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG/UTMASTG = TMA, LDGMC/STGMC... = multimem, REDG = red.global).
+(UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG/UTMASTG = TMA, multimem forms, REDG = red.global).
 Runs on the CPU box (no GPU needed):  python bench/dump_sass.py"""
 import collections
 import os
@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "distributed_resnet_tensorflow_b200", "_native", "libdrn_b200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
 INTERESTING = re.compile(r"^(UTC\w+|LDTM|STTM|UTMA\w+|UBLKCP|SYNCS|REDG|RED|ATOMG|ATOMS|ATOM|LDGMC|STGMC|REDGMC|LDG|STG|"
-                         r"F2FP|HMMA|ACQBULK|PREEXIT|UCGABAR|MEMBAR|CCTL|FENCE|ERRBAR|NANOSLEEP|LDS|STS|MUFU)")
+                         r"F2FP|HMMA|ACQBULK|PREEXIT|UCGABAR|MEMBAR|CCTL|FENCE|ERRBAR|NANOSLEEP|MUFU)")
 
 
 def demangle(names):
@@ -30,12 +30,11 @@ def short(dem):
 
 def main():
     sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
-    funcs, cur, name = {}, None, None
+    funcs, cur = {}, None
     for line in sass.splitlines():
         m = re.match(r"\s*Function : (\S+)", line)
         if m:
-            name = m.group(1)
-            cur = funcs.setdefault(name, [])
+            cur = funcs.setdefault(m.group(1), [])
         if cur is not None:
             cur.append(line)
     dem = demangle(list(funcs))
@@ -43,14 +42,16 @@ def main():
     for mangled, lines in funcs.items():
         base, targs = short(dem[mangled])
         ops = collections.Counter()
+        n_inst = 0
         for ln in lines:
-            m = re.match(r"\s*/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]*)", ln)
-            if m:
-                op = m.group(1)
-                if INTERESTING.match(op):
-                    key = op if op.startswith(("UTC", "UTMA", "LDGMC", "STGMC")) else op.split(".")[0]
-                    ops[key] += 1
-        n_inst = sum(1 for ln in lines if re.match(r"\s*/\*[0-9a-f]{4}\*/", ln))
+            m = re.match(r"\s*/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]*)", ln)
+            if not m:
+                continue
+            n_inst += 1
+            op = m.group(1)
+            if INTERESTING.match(op):
+                keep_full = op.startswith(("UTC", "UTMA", "LDGMC", "STGMC")) or ".MC" in op
+                ops[op if keep_full else op.split(".")[0]] += 1
         fam[base].append((n_inst, targs, ops, lines))
     os.makedirs(OUT, exist_ok=True)
     for f in os.listdir(OUT):
@@ -60,8 +61,7 @@ def main():
     for base in sorted(fam):
         insts = sorted(fam[base], key=lambda t: -t[0])
         n_inst, targs, ops, lines = insts[0]
-        path = os.path.join(OUT, base + ".sass")
-        with open(path, "w") as f:
+        with open(os.path.join(OUT, base + ".sass"), "w") as f:
             f.write(f"// {base}{targs}: largest of {len(insts)} instantiation(s), {n_inst} instructions\n")
             f.write("\n".join(lines) + "\n")
         for n_inst_i, targs_i, ops_i, _ in insts:
@@ -72,15 +72,13 @@ def main():
                 "listed below with its instruction count and the mnemonics that identify the hardware paths:\n"
                 "`UTCHMMA` = tcgen05.mma (`.2CTA` = cta_group::2), `LDTM` = tcgen05.ld, `UTMALDG`/`UTMASTG` = TMA\n"
                 "load/store (`.IM2COL`, `.2CTA`), `UTCBAR` = tcgen05.commit, `UTCATOMSWS` = TMEM allocation,\n"
-                "`SYNCS` = mbarrier, `REDG` = red.global, `LDGMC`/`STGMC` (or `.MC` forms) = multimem.ld_reduce /\n"
-                "multimem.st through the NVSwitch, `ACQBULK`/`PREEXIT` = griddepcontrol, `F2FP` = packed bf16\n"
-                "conversion.  No `HMMA` (mma.sync) appears anywhere.\n\n"
+                "`SYNCS` = mbarrier, `REDG` = red.global, `LDGMC` / `.MC` forms = multimem.ld_reduce / multimem.st\n"
+                "through the NVSwitch, `ACQBULK`/`PREEXIT` = griddepcontrol, `F2FP` = packed bf16 conversion.\n\n"
                 "| kernel | template arguments | instructions | mnemonics |\n|---|---|---|---|\n")
         for base, targs, n_inst, ops in rows:
             desc = ", ".join(f"{k}x{v}" for k, v in sorted(ops.items()))
             f.write(f"| `{base}` | `{targs[:90]}` | {n_inst} | {desc} |\n")
-        any_hmma = any("HMMA" in ops for _, _, _, ops in rows)
-        f.write(f"\nHMMA present: {any_hmma}\n")
+        f.write(f"\nHMMA (mma.sync) present anywhere: {any('HMMA' in ops for _, _, _, ops in rows)}\n")
     print(f"{len(funcs)} kernels, {len(fam)} families -> {OUT}")
 
 

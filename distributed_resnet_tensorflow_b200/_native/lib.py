@@ -51,6 +51,7 @@ _SIGNATURES = {
     "drn_watchdog_status": (_i, []),
     "drn_watchdog_arm": (_i, []),
     "drn_num_sms": (_i, []),
+    "drn_set_pdl_mask": (_i, [_i]),
     "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
     "drn_conv_igemm_ex": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, ctypes.POINTER(PullDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),

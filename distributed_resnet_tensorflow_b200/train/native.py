@@ -106,6 +106,9 @@ class NativeTrainer:
         self._hyper_done = [None] * 8
         self._hyper_next = 0
         _nl.check(_nl.load().drn_watchdog_arm(), "drn_watchdog_arm")
+        # launch-bound CIFAR-sized steps: let each convolution kernel's set-up overlap its predecessor's
+        # tail (programmatic dependent launch; measured 516 -> 536 steps/s at batch 128, 922 -> 967 at 16)
+        _nl.load().drn_set_pdl_mask(2 if spec.dataset != "imagenet" else -1)
         self.steps_done = 0
         self.h2d_bytes_per_step = batch * img_bytes + batch * 4 + batch * 12
         self.d2h_bytes_per_step = 4 * 4 + 4

@@ -29,6 +29,10 @@ int drn_watchdog_status(void);
  * made the CUDA context unusable. (the reference relies on session re-creation.) */
 int drn_watchdog_arm(void);
 int drn_num_sms(void);
+/* Programmatic dependent launch (griddepcontrol) for the library's launches: bit 0 = element-wise /
+ * pooling / optimizer kernels, bit 1 = tcgen05 convolution kernels, -1 = default (off).  Pays for
+ * launch-bound steps (CIFAR-sized layers: +4 % steps/s), costs throughput on ImageNet-sized ones. */
+int drn_set_pdl_mask(int mask);
 
 /* ---------------------------------------------------------------------------------------------
  * Convolution (reference: tf.layers.conv2d in resnet_model_official.py:80-91; ops K1-K4)
