@@ -17,7 +17,9 @@ INTERESTING = re.compile(r"^(UTC\w+|LDTM|STTM|UTMA\w+|UBLKCP|SYNCS|REDG|RED|ATOM
 
 
 def demangle(names):
-    out = subprocess.run(["c++filt"], input="\n".join(names), capture_output=True, text=True).stdout.splitlines()
+    # file-local kernels carry a "__nv_static_NN__<hash>_<file>__" prefix in front of the Itanium name
+    stripped = [n[n.index("_ZN"):] if "_ZN" in n else n for n in names]
+    out = subprocess.run(["c++filt"], input="\n".join(stripped), capture_output=True, text=True).stdout.splitlines()
     return dict(zip(names, out))
 
 
@@ -40,11 +42,13 @@ def main():
     dem = demangle(list(funcs))
     fam = collections.defaultdict(list)
     for mangled, lines in funcs.items():
+        if mangled.startswith(("__cuda_", "_INTERNAL_")) or "_kernel" not in mangled:
+            continue                                   # compiler helpers (division slow paths, traps)
         base, targs = short(dem[mangled])
         ops = collections.Counter()
         n_inst = 0
         for ln in lines:
-            m = re.match(r"\s*/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]*)", ln)
+            m = re.match(r"\s*/\*[0-9a-f]{4,6}\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]*)", ln)
             if not m:
                 continue
             n_inst += 1
@@ -63,7 +67,9 @@ def main():
         n_inst, targs, ops, lines = insts[0]
         with open(os.path.join(OUT, base + ".sass"), "w") as f:
             f.write(f"// {base}{targs}: largest of {len(insts)} instantiation(s), {n_inst} instructions\n")
-            f.write("\n".join(lines) + "\n")
+            # keep the instruction text, drop the encoding words (halves the size)
+            f.write("\n".join(re.sub(r"\s*/\* 0x[0-9a-f]{16} \*/\s*$", "", ln) for ln in lines
+                              if not re.match(r"^\s*/\* 0x[0-9a-f]{16} \*/\s*$", ln)) + "\n")
         for n_inst_i, targs_i, ops_i, _ in insts:
             rows.append((base, targs_i, n_inst_i, ops_i))
     with open(os.path.join(OUT, "SUMMARY.md"), "w") as f:
