@@ -93,3 +93,33 @@ def test_gpu_jpeg_input_path_matches_the_host_path(tmp_path, decoder):
             assert np.array_equal(hl, dl) and np.array_equal(hc, dc)
             diff = np.abs(di.cpu().numpy().astype(np.int32) - hi.astype(np.int32))
             assert diff.mean() < 1.5 and np.percentile(diff, 99) <= 8, (diff.mean(), diff.max())
+
+
+@pytest.mark.parametrize("pull", ["push", "pull"])
+def test_two_worker_parameter_server_cli_saves_timed_checkpoints(tmp_path, pull):
+    """resnet_cifar_main.py as two --job_name=worker processes on two GPUs (native backend: parameter
+    shard i lives on worker i's GPU), both weight paths, with the reference's time-based checkpoint
+    hook (every worker joins the collective save the chief's clock asks for) and an evaluation of
+    the result by a separate process."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from distributed_resnet_tensorflow_b200.ckpt.saver import Saver, latest_checkpoint
+    root = str(tmp_path / "ckpt")
+    port = 24000 + os.getpid() % 2000
+    common = [os.path.join(ROOT, "resnet_cifar_main.py"), "--job_name=worker", "--sync_replicas=True",
+              f"--ps_hosts=localhost:{port + 500},localhost:{port + 501}",
+              f"--worker_hosts=localhost:{port},localhost:{port + 1}", "--resnet_size=8", "--batch_size=32",
+              "--num_gpus=2", f"--log_root={root}", "--log_every=25", "--train_steps=900", "--base_lr=0.05",
+              "--save_checkpoint_secs=1", f"--ps_pull={pull}", f"--eval_dir={tmp_path / 'ev'}"]
+    procs = [subprocess.Popen([sys.executable] + common + [f"--task_index={i}"], cwd=ROOT, stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True) for i in range(2)]
+    outs = [p.communicate(timeout=600)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o[-3000:]
+    assert "mode=ps backend=native" in outs[0] and "step = 900" in outs[0] and "step = 900" in outs[1]
+    assert outs[0].count("saved checkpoint") >= 2, outs[0][-2000:]
+    v = Saver.restore(latest_checkpoint(root))
+    assert int(v["global_step"]) == 900
+    prec = float(outs[0].split("step = 900,")[1].split("precision = ")[1].split(",")[0])
+    assert prec > 0.5, outs[0][-800:]

@@ -94,6 +94,26 @@ def test_one_ps_two_workers_sync_replicas(tmp_path):
 
 
 @pytest.mark.slow
+def test_parameter_server_mode_saves_time_based_checkpoints(tmp_path):
+    """MonitoredTrainingSession saves every save_checkpoint_secs in PS mode too (resnet_cifar_main.py:329);
+    with sharded state the save is a collective, so the chief's clock is broadcast to the workers."""
+    root = str(tmp_path / "ckpt")
+    port = 27000 + os.getpid() % 2000
+    common = [f"--ps_hosts=localhost:{port + 500}", f"--worker_hosts=localhost:{port},localhost:{port + 1}",
+              "--sync_replicas=True", f"--resnet_size={SIZE}", f"--batch_size={BATCH}", "--train_steps=90",
+              "--num_gpus=0", f"--log_root={root}", "--log_every=2", "--backend=torch", "--num_intra_threads=1",
+              "--save_checkpoint_secs=1"]
+    py = [sys.executable, os.path.join(ROOT, "resnet_cifar_main.py")]
+    outs = _run([py + ["--job_name=ps", "--task_index=0"] + common,
+                 py + ["--job_name=worker", "--task_index=0"] + common,
+                 py + ["--job_name=worker", "--task_index=1"] + common])
+    saved = [l for l in outs[1].splitlines() if "saved checkpoint" in l]
+    assert len(saved) >= 2, outs[1][-2000:]          # at least one timed save before the final one
+    assert "saved checkpoint" not in outs[2]         # only the chief writes
+    assert int(Saver.restore(latest_checkpoint(root))["global_step"]) == 90
+
+
+@pytest.mark.slow
 def test_two_rank_allreduce_matches_parameter_server(tmp_path):
     root = str(tmp_path / "ckpt")
     port = 25000 + os.getpid() % 2000
