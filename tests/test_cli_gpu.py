@@ -110,16 +110,16 @@ def test_two_worker_parameter_server_cli_saves_timed_checkpoints(tmp_path, pull)
     common = [os.path.join(ROOT, "resnet_cifar_main.py"), "--job_name=worker", "--sync_replicas=True",
               f"--ps_hosts=localhost:{port + 500},localhost:{port + 501}",
               f"--worker_hosts=localhost:{port},localhost:{port + 1}", "--resnet_size=8", "--batch_size=32",
-              "--num_gpus=2", f"--log_root={root}", "--log_every=25", "--train_steps=900", "--base_lr=0.05",
+              "--num_gpus=2", f"--log_root={root}", "--log_every=500", "--train_steps=9000", "--base_lr=0.05",
               "--save_checkpoint_secs=1", f"--ps_pull={pull}", f"--eval_dir={tmp_path / 'ev'}"]
     procs = [subprocess.Popen([sys.executable] + common + [f"--task_index={i}"], cwd=ROOT, stdout=subprocess.PIPE,
                               stderr=subprocess.STDOUT, text=True) for i in range(2)]
     outs = [p.communicate(timeout=600)[0] for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o[-3000:]
-    assert "mode=ps backend=native" in outs[0] and "step = 900" in outs[0] and "step = 900" in outs[1]
+    assert "mode=ps backend=native" in outs[0] and "step = 9000" in outs[0] and "step = 9000" in outs[1]
     assert outs[0].count("saved checkpoint") >= 2, outs[0][-2000:]
     v = Saver.restore(latest_checkpoint(root))
-    assert int(v["global_step"]) == 900
-    prec = float(outs[0].split("step = 900,")[1].split("precision = ")[1].split(",")[0])
+    assert int(v["global_step"]) == 9000
+    prec = float(outs[0].split("step = 9000,")[1].split("precision = ")[1].split(",")[0])
     assert prec > 0.5, outs[0][-800:]
