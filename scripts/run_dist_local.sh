@@ -20,16 +20,28 @@ ps_hosts=""; for ((j=0; j<NUM_PS; j++)); do ps_hosts+="${ps_hosts:+,}localhost:$
 wk_hosts=""; for ((i=0; i<NUM_WK; i++)); do wk_hosts+="${wk_hosts:+,}localhost:$((2220+i))"; done
 COMMON="--ps_hosts=$ps_hosts --worker_hosts=$wk_hosts --sync_replicas=True --batch_size=$BATCH \
  --train_steps=$STEPS --num_gpus=$NGPU --log_root=$LOGDIR/ckpt --train_dir=$LOGDIR/train --eval_dir=$LOGDIR/train $*"
-pids=()
-for ((j=0; j<NUM_PS; j++)); do
-  CUDA_VISIBLE_DEVICES= $PYTHON "$HERE/$SCRIPT" --job_name=ps --task_index=$j $COMMON > "$LOGDIR/ps$j.log" 2>&1 &
-  pids+=($!)
+# A worker that loses a peer inside an in-kernel collective leaves with exit code 86 (watchdog ->
+# CollectiveTimeout, train/loop.py); the launcher then stops the remaining tasks (their own PIDs) and
+# starts the whole job again - it resumes from the latest checkpoint in $LOGDIR/ckpt, which is what
+# MonitoredTrainingSession's session re-creation does for the reference. TF_MAX_RESTARTS (default 3).
+MAX_RESTARTS=${TF_MAX_RESTARTS:-3}
+attempt=0
+while :; do
+  pids=()
+  for ((j=0; j<NUM_PS; j++)); do
+    CUDA_VISIBLE_DEVICES= $PYTHON "$HERE/$SCRIPT" --job_name=ps --task_index=$j $COMMON >> "$LOGDIR/ps$j.log" 2>&1 &
+    pids+=($!)
+  done
+  for ((i=0; i<NUM_WK; i++)); do
+    $PYTHON "$HERE/$SCRIPT" --job_name=worker --task_index=$i $COMMON >> "$LOGDIR/wk$i.log" 2>&1 &
+    pids+=($!)
+  done
+  echo "started ${#pids[@]} tasks (pids ${pids[*]}); logs in $LOGDIR"
+  printf '%s\n' "${pids[@]}" > "$LOGDIR/pids"
+  rc=0; for p in "${pids[@]}"; do wait "$p" || { r=$?; [ $rc -eq 86 ] || rc=$r; [ $r -eq 86 ] && for q in "${pids[@]}"; do kill "$q" 2>/dev/null || true; done; }; done
+  if [ $rc -eq 86 ] && [ $attempt -lt $MAX_RESTARTS ]; then
+    attempt=$((attempt+1)); echo "collective timeout (exit 86): restart $attempt/$MAX_RESTARTS from the latest checkpoint"
+    rm -f "$LOGDIR/ckpt/train.done"; sleep 2; continue
+  fi
+  exit $rc
 done
-for ((i=0; i<NUM_WK; i++)); do
-  $PYTHON "$HERE/$SCRIPT" --job_name=worker --task_index=$i $COMMON > "$LOGDIR/wk$i.log" 2>&1 &
-  pids+=($!)
-done
-echo "started ${#pids[@]} tasks (pids ${pids[*]}); logs in $LOGDIR"
-printf '%s\n' "${pids[@]}" > "$LOGDIR/pids"
-rc=0; for p in "${pids[@]}"; do wait "$p" || rc=$?; done
-exit $rc
