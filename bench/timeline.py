@@ -8,13 +8,14 @@ from distributed_resnet_tensorflow_b200.models.init import init_variables
 from distributed_resnet_tensorflow_b200.models.spec import build_spec
 from distributed_resnet_tensorflow_b200.train.native import NativeTrainer
 
-def main(batch=128, out="gpurun_out/timeline.csv"):
-    spec = build_spec("imagenet", 50)
+def main(batch=128, out="gpurun_out/timeline.csv", dataset="imagenet"):
+    spec = build_spec(dataset, 50)
     tr = NativeTrainer(spec, batch, device="cuda:0", weight_decay=1e-4, use_graph=True)
     tr.import_variables(init_variables(spec, seed=0))
     rng = np.random.default_rng(0)
-    imgs = torch.from_numpy(rng.integers(0, 256, size=(batch, 224 * 224 * 3), dtype=np.uint8)).pin_memory()
-    labs = torch.from_numpy(rng.integers(0, 1001, size=(batch,), dtype=np.int32)).pin_memory()
+    nbytes = 224 * 224 * 3 if dataset == "imagenet" else 3072
+    imgs = torch.from_numpy(rng.integers(0, 256, size=(batch, nbytes), dtype=np.uint8)).pin_memory()
+    labs = torch.from_numpy(rng.integers(0, spec.num_classes, size=(batch,), dtype=np.int32)).pin_memory()
     for _ in range(5):
         tr.train_step(imgs, labs, lr=0.1)
     torch.cuda.synchronize()
@@ -33,9 +34,11 @@ def main(batch=128, out="gpurun_out/timeline.csv"):
         w = csv.writer(f); w.writerow(["name", "stream", "start_us", "dur_us"]); w.writerows(rows)
     print("events", len(rows))
     try:
-        prof.export_chrome_trace("gpurun_out/trace.json")
+        prof.export_chrome_trace(out.replace(".csv", ".json"))
     except Exception as e:
         print("trace export failed", e)
 
 if __name__ == "__main__":
-    main()
+    ds = sys.argv[1] if len(sys.argv) > 1 else "imagenet"
+    b = int(sys.argv[2]) if len(sys.argv) > 2 else 128
+    main(batch=b, out=f"gpurun_out/timeline_{ds}_{b}.csv", dataset=ds)

@@ -718,7 +718,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
       if (acc == 0) acc_phase ^= 1;
     }
     flush_stats(cur_n_tile);
-    if (leader) tma_store_wait_all<0>();
+    // the staging buffers must outlive the stores' READS only; completion of the writes is part of
+    // grid completion (what the next kernel in the stream, or griddepcontrol.wait, orders behind)
+    if (leader) tma_store_wait_read<0>();
   }
 
   tc_fence_before();

@@ -131,7 +131,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
       if (elect_one()) {
         int stage = 0;
         uint32_t phase = 0;
-        const uint32_t tx_bytes = C_::kABytes + nboxes * C_::kBBoxBytes;
+        // dY boxes that lie entirely beyond Cout are not fetched at all (their rows of the 128-row
+        // UMMA tile then hold stale shared memory: those accumulator rows are never written out)
+        int a_boxes = (p.Kout - co_tile * 128 + CWA - 1) / CWA;
+        if (a_boxes > C_::kABoxes) a_boxes = C_::kABoxes;
+        const uint32_t tx_bytes = a_boxes * C_::kABoxBytes + nboxes * C_::kBBoxBytes;
         // first box of this CTA's column window (constant over the pixel loop): no divisions inside
         const int tap0 = n0 / p.C, c00 = n0 - tap0 * p.C;
         const int r0 = tap0 / p.S, s0 = tap0 - r0 * p.S;
@@ -154,8 +158,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
           mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
 #pragma unroll
           for (int i = 0; i < C_::kABoxes; ++i)
-            tma_load_2d(a_dst + i * C_::kABoxBytes, &tmapDY, full_bar(stage),
-                        co_tile * 128 + i * CWA, m0);
+            if (i < a_boxes)
+              tma_load_2d(a_dst + i * C_::kABoxBytes, &tmapDY, full_bar(stage),
+                          co_tile * 128 + i * CWA, m0);
           int c0 = c00, r = r0, s = s0;
           for (int i = 0; i < nboxes; ++i) {
             tma_load_im2col_4d(b_dst + i * C_::kBBoxBytes, &tmapX, full_bar(stage), c0, w0, h0, img,
