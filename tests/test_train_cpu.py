@@ -108,3 +108,44 @@ def test_resnet_single_train_eval_mode(tmp_path):
     out = res.stdout + res.stderr
     assert res.returncode == 0, out[-3000:]
     assert "total trainable parameters" in out and out.count("best precision") == 2 and "step = 6" in out
+
+
+def test_prefetcher_keeps_order_drops_short_batches_and_forwards_errors():
+    """The input thread of the training loop (train/loop.py:_Prefetcher)."""
+    import numpy as np
+    from distributed_resnet_tensorflow_b200.train.loop import _Prefetcher
+
+    def batches(n, bad_at=None):
+        for i in range(n):
+            if bad_at is not None and i == bad_at:
+                raise ValueError("reader failed")
+            size = 4 if i != 2 else 3          # one short batch (end of an epoch)
+            yield np.full((size, 2), i), np.arange(size), None
+
+    seen = []
+    pf = _Prefetcher(batches(6), 4, lambda b: ("prepared", int(b[0][0, 0])))
+    while True:
+        item = pf.next()
+        if item is None:
+            break
+        seen.append(item)
+    pf.close()
+    assert seen == [("prepared", i) for i in (0, 1, 3, 4, 5)]
+    pf = _Prefetcher(batches(6, bad_at=1), 4, lambda b: b)
+    assert pf.next()[0][0, 0] == 0
+    import pytest
+    with pytest.raises(ValueError):
+        pf.next()
+    pf.close()
+
+
+def test_new_flags_reach_the_config():
+    from distributed_resnet_tensorflow_b200 import config as C
+    from distributed_resnet_tensorflow_b200.utils import flags as F
+    v, _ = F.make_flagset(**F.IMAGENET_MAIN).parse(["--ps_pull=pull", "--input_workers=6", "--allreduce_algo=oneshot_p2p",
+                                                    "--resnet_version=1"])
+    cfg = C.from_flags(v)
+    assert cfg.train.ps_pull == "pull" and cfg.train.input_workers == 6
+    assert cfg.train.allreduce_algo == "oneshot_p2p" and cfg.model.resnet_version == 1
+    cfg = C.from_flags(F.make_flagset().parse([])[0])
+    assert cfg.train.ps_pull == "push" and cfg.train.input_workers == 0 and cfg.train.allreduce_algo == "auto"
