@@ -33,10 +33,14 @@ def cifar_main(argv: Optional[Sequence[str]] = None):
 
 
 def cifar_main_horovod(argv: Optional[Sequence[str]] = None):
-    """resnet_cifar_main_horovod.py: allreduce CIFAR training (run under torchrun / mpirun-style
-    launchers; pass --use_horovod=True as with the reference)."""
+    """resnet_cifar_main_horovod.py: allreduce CIFAR training under a one-process-per-GPU launcher
+    (torchrun / mpirun / srun: rank and world size come from the launcher's environment, the
+    counterpart of hvd.init(), resnet_cifar_main_horovod.py:342).  The only difference from cifar_main
+    is that this entry point IS the allreduce path: --use_horovod defaults to True here (the reference
+    needs the flag passed explicitly, scripts/submit-horovod-train-mac.sh:5); everything else - flags,
+    hooks, checkpoints - is the shared training loop."""
     _setup_logging()
-    cfg = _parse(argv, _flags.CIFAR_MAIN, "train")
+    cfg = _parse(argv, _flags.CIFAR_MAIN, "train", use_horovod=True)
     if cfg.mode != "train":
         return {}
     from ..train.loop import train

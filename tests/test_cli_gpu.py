@@ -45,6 +45,19 @@ def test_cifar_train_eval_resume_native(tmp_path):
     assert "restored" in out2 and "step = 100" in out2
 
 
+def test_v1_networks_train_and_evaluate_through_the_cli(tmp_path):
+    """--resnet_version=1 (post-activation) on the native backend: train, checkpoint, evaluate."""
+    root = str(tmp_path / "ckpt")
+    out = _run([os.path.join(ROOT, "resnet_cifar_main.py"), "--resnet_version=1", "--resnet_size=14", "--batch_size=64",
+                "--num_gpus=1", f"--log_root={root}", "--train_steps=80", "--log_every=20", "--base_lr=0.05"])
+    assert "backend=native" in out and "step = 80" in out
+    prec = float(out.split("step = 80,")[1].split("precision = ")[1].split(",")[0])
+    assert prec > 0.5, out[-800:]
+    ev = _run([os.path.join(ROOT, "resnet_cifar_eval.py"), "--resnet_version=1", "--resnet_size=14", "--num_gpus=1",
+               f"--log_root={root}", "--eval_once=True", "--eval_batch_count=5"])
+    assert "best precision" in ev
+
+
 def test_imagenet_main_serial_native(tmp_path):
     out = _run([os.path.join(ROOT, "resnet_imagenet_main.py"), "--resnet_size=18", "--batch_size=16", "--num_gpus=1",
                 "--train_steps=12", "--log_every=4", f"--log_root={tmp_path / 'ckpt'}", f"--train_dir={tmp_path / 'tr'}"])
