@@ -221,7 +221,9 @@ ps_update_kernel(PeerPtrs grads, float4* __restrict__ mc_grads, PeerPtrs shadows
       float4 g;
       if constexpr (kMC) {
         g = mc_ld_reduce_f4(mc_grads + j);
-        mc_st_zero_f4(mc_grads + j, zero_after(g.x));   // accumulators taken: clear all N at once
+        // pull mode has no closing barrier behind which the replicas could clear their own
+        // accumulators: the owner clears all N copies with one multicast store
+        if constexpr (kPull) mc_st_zero_f4(mc_grads + j, zero_after(g.x));
       } else {
         g = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 8
@@ -233,7 +235,7 @@ ps_update_kernel(PeerPtrs grads, float4* __restrict__ mc_grads, PeerPtrs shadows
           g.y += v.y;
           g.z += v.z;
           g.w += v.w;
-          st_f4(gp, make_float4(0.f, 0.f, 0.f, 0.f));  // accumulator taken: clear it for the next step
+          if constexpr (kPull) st_f4(gp, make_float4(0.f, 0.f, 0.f, 0.f));  // accumulator taken: clear it
         }
       }
       float4 w = master[j], m = mom[j];
@@ -286,6 +288,12 @@ ps_update_kernel(PeerPtrs grads, float4* __restrict__ mc_grads, PeerPtrs shadows
     }
   } else {
     block_barrier(pads, rank, nranks, channel);  // new weights are visible on every worker
+    // every owner has taken its slice of my accumulators: clear my whole range locally (HBM traffic
+    // only - clearing from the owners' side would put another (N-1)/N * S bytes on the links)
+    float4* mine = reinterpret_cast<float4*>(grads.p[rank]) + off4;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride)
+      mine[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
 }
 

@@ -79,12 +79,16 @@ struct PrepEntry {
   long long src_off, dst_off;  // element offsets into the bf16 weight arena / the dgrad-bank arena
   int K, RS, C, tile_begin;    // tile_begin = first block index of this layer
 };
-__global__ void weight_prep_dgrad_batched_kernel(const __nv_bfloat16* __restrict__ src_base,
-                                                 __nv_bfloat16* __restrict__ dst_base,
-                                                 const PrepEntry* __restrict__ table, int n_layers) {
+__global__ void __launch_bounds__(256)
+weight_prep_dgrad_batched_kernel(const __nv_bfloat16* __restrict__ src_base,
+                                 __nv_bfloat16* __restrict__ dst_base,
+                                 const PrepEntry* __restrict__ table, int n_layers) {
   pdl_trigger();
   pdl_wait();
-  __shared__ __nv_bfloat16 tile[32][33];
+  // 64 x 64 tiles moved with 4-byte accesses: a warp reads / writes 128 contiguous bytes of a row
+  // (the 32 x 32 tiles with 2-byte accesses of the first version moved 64-byte segments: 100 us
+  // for the 23.5 M weights of ResNet-50 where ~30 us of traffic is needed)
+  __shared__ uint32_t tile[64][33];
   // binary search: last layer whose tile_begin <= blockIdx.x
   int lo = 0, hi = n_layers - 1;
   while (lo < hi) {
@@ -93,22 +97,30 @@ __global__ void weight_prep_dgrad_batched_kernel(const __nv_bfloat16* __restrict
   }
   const PrepEntry e = table[lo];
   int t = blockIdx.x - e.tile_begin;
-  const int ct = (e.C + 31) / 32, kt = (e.K + 31) / 32;
-  const int c0 = (t % ct) * 32;
+  const int ct = (e.C + 63) / 64, kt = (e.K + 63) / 64;
+  const int c0 = (t % ct) * 64;
   t /= ct;
-  const int k0 = (t % kt) * 32;
+  const int k0 = (t % kt) * 64;
   const int tap = t / kt;
   const __nv_bfloat16* src = src_base + e.src_off;
   __nv_bfloat16* dst = dst_base + e.dst_off;
-  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
-    const int k = k0 + j, c = c0 + threadIdx.x;
-    if (k < e.K && c < e.C) tile[j][threadIdx.x] = src[((long long)k * e.RS + tap) * e.C + c];
+  const int tx = threadIdx.x, ty = threadIdx.y;   // (32, 8)
+  for (int j = ty; j < 64; j += 8) {
+    const int k = k0 + j, c = c0 + 2 * tx;
+    uint32_t v = 0u;
+    if (k < e.K && c < e.C)     // C is even: a pair is in range or out of range as a whole
+      v = *reinterpret_cast<const uint32_t*>(src + ((long long)k * e.RS + tap) * e.C + c);
+    tile[j][tx] = v;
   }
   __syncthreads();
-  const int ftap = e.RS - 1 - tap;
-  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
-    const int c = c0 + j, k = k0 + threadIdx.x;
-    if (k < e.K && c < e.C) dst[((long long)c * e.RS + ftap) * e.K + k] = tile[threadIdx.x][j];
+  const int ftap = e.RS - 1 - tap;  // flipping r and s together reverses the linear tap index
+  const unsigned short* t16 = reinterpret_cast<const unsigned short*>(&tile[0][0]);
+  for (int j = ty; j < 64; j += 8) {
+    const int c = c0 + j, k = k0 + 2 * tx;
+    if (c < e.C && k < e.K) {   // K is even as well
+      const uint32_t lo16 = t16[(2 * tx) * 66 + j], hi16 = t16[(2 * tx + 1) * 66 + j];
+      *reinterpret_cast<uint32_t*>(dst + ((long long)c * e.RS + ftap) * e.K + k) = lo16 | (hi16 << 16);
+    }
   }
 }
 

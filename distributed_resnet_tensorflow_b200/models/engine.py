@@ -488,7 +488,7 @@ class NativeResNet:
             else:
                 K, RS, C = e.dev_shape[0], e.dev_shape[1] * e.dev_shape[2], e.dev_shape[3]
             rows.append((e.offset, dst_off, K, RS, C, tiles))
-            tiles += RS * ((K + 31) // 32) * ((C + 31) // 32)
+            tiles += RS * ((K + 63) // 64) * ((C + 63) // 64)
         tab = np.zeros(len(rows), dtype=[("src", "<i8"), ("dst", "<i8"), ("K", "<i4"), ("RS", "<i4"),
                                          ("C", "<i4"), ("tb", "<i4")])
         for i, r in enumerate(rows):

@@ -247,7 +247,7 @@ int drn_weight_prep_dgrad(const void* w_krsc, void* w_dgrad, int K, int R, int S
                           void* stream);
 /* the same for many layers in one launch; table = device array of {int64 src_off, int64 dst_off,
  * int32 K, RS, C, tile_begin} (offsets in elements; tile_begin = running sum of
- * RS*ceil(K/32)*ceil(C/32)), total_tiles = grand total */
+ * RS*ceil(K/64)*ceil(C/64)), total_tiles = grand total; K and C even */
 int drn_weight_prep_dgrad_batched(const void* w_arena, void* dgrad_arena, const void* table,
                                   int n_layers, int total_tiles, void* stream);
 /* out[n, p*stride, q*stride, :] = dy[n, p, q, :], zero elsewhere; out is [N,U,V,C] */

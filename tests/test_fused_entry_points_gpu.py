@@ -182,7 +182,7 @@ def test_batched_dgrad_bank_prep_equals_per_layer_prep():
         r = int(round(rs ** 0.5))
         nl.call("drn_weight_prep_dgrad", arena.data_ptr() + 2 * off, want.data_ptr() + 2 * off, k, r, r, c, _st())
         rows.append((off, off, k, rs, c, tiles))
-        tiles += rs * ((k + 31) // 32) * ((c + 31) // 32)
+        tiles += rs * ((k + 63) // 64) * ((c + 63) // 64)
         off += k * rs * c
     table = np.zeros(len(rows), dtype=np.dtype([("s", "<i8"), ("d", "<i8"), ("k", "<i4"), ("rs", "<i4"),
                                                 ("c", "<i4"), ("t", "<i4")]))
