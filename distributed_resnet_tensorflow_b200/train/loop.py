@@ -423,7 +423,16 @@ class _Prefetcher:
         return None
 
     def close(self) -> None:
+        """Stop the thread and wait for it: a daemon thread that is still inside numpy / a reader when the
+        interpreter shuts down can take the process down with it."""
         self._stop.set()
+        try:
+            while True:
+                self._q.get_nowait()
+        except queue.Empty:
+            pass
+        if self._thread is not threading.current_thread():
+            self._thread.join(timeout=10.0)
 
 
 def _save(be, saver: Optional[Saver], ctx: DistContext) -> None:
