@@ -165,6 +165,11 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+__device__ __forceinline__ void red_add_v4_f32(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
 // generic-proxy writes to ANY state space (here: global memory another CTA filled and published with
 // a release) -> ordered before this thread's later async-proxy reads (TMA loads)
 __device__ __forceinline__ void fence_proxy_async_all() {
