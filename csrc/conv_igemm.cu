@@ -870,7 +870,12 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
     tR2 = tR;
   }
 
-  int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
+  // DRN_IGEMM_SMS (experiment): persistent CTAs of the dependent chain on fewer SMs, leaving the rest to
+  // the filter gradients of the second stream.  Measured: monotonically slower (14 737 / 14 646 / 14 615 /
+  // 14 409 / 14 214 img/s at 148 / 140 / 132 / 124 / 112 SMs)
+  int sm_cap = env_int("DRN_IGEMM_SMS", 0);
+  if (sm_cap <= 0 || sm_cap > num_sms()) sm_cap = num_sms();
+  int grid = p.total_tiles < sm_cap ? p.total_tiles : sm_cap;
   p.pre_ss = reinterpret_cast<const float2*>(current_pre());
   if (current_pull() != nullptr) p.pull = *static_cast<const PullArgs*>(current_pull());
   else memset(&p.pull, 0, sizeof(p.pull));
