@@ -28,10 +28,17 @@ def main(n=1024, batch=128):
     arms = [("host, 5 threads (reference's num_threads=5)", im.ImageNetBatches, {}),
             (f"host, {min(8, ncpu)} reader processes x 5 threads", im.MultiProcessBatches, {"workers": min(8, ncpu)}),
             ("device, torchvision nvJPEG binding", im.ImageNetBatchesGPU, {"device": "cuda:0", "decoder": "torchvision"}),
-            ("device, libdrn nvJPEG binding (csrc/jpeg.cu)", im.ImageNetBatchesGPU, {"device": "cuda:0", "decoder": "native"})]
+            ("device, libdrn nvJPEG binding (csrc/jpeg.cu), 1 decoder thread", im.ImageNetBatchesGPU,
+             {"device": "cuda:0", "decoder": "native", "decode_threads": 1}),
+            ("device, libdrn nvJPEG binding, 3 decoder threads", im.ImageNetBatchesGPU,
+             {"device": "cuda:0", "decoder": "native", "decode_threads": 3}),
+            ("device, libdrn nvJPEG binding, 6 decoder threads", im.ImageNetBatchesGPU,
+             {"device": "cuda:0", "decoder": "native", "decode_threads": 6, "num_threads": 8}),
+            ("device, libdrn nvJPEG binding, 10 decoder threads", im.ImageNetBatchesGPU,
+             {"device": "cuda:0", "decoder": "native", "decode_threads": 10, "num_threads": 8})]
     for name, cls, kw in arms:
         try:
-            obj = cls(d, batch, True, 3, seed=1, files=[shard] if cls is not im.MultiProcessBatches else shards, **kw)
+            obj = cls(d, batch, True, 6, seed=1, files=[shard] if cls is not im.MultiProcessBatches else shards, **kw)
         except Exception as e:
             print(f"{name}: unavailable ({e!r})"); continue
         it = iter(obj)
