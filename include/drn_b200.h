@@ -289,6 +289,10 @@ int drn_jpeg_info(void* handle, const unsigned char* const* data, const size_t* 
 int drn_jpeg_decode_batch(void* handle, const unsigned char* const* data, const size_t* lengths, int B,
                           void* const* out, const int* wh, int* status, void* stream);
 
+/* Measurement probe (csrc/probe_tma.cu, bench/probe_tma.py; not used by the framework): persistent TMA
+ * copy of a [rows][cols] bf16 matrix in boxes of 128 rows x box_cols (32 or 64) columns. */
+int drn_probe_tma_copy(const void* src, void* dst, long long rows, int cols, int box_cols, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Host utilities (no GPU): CRC-32C (Castagnoli) used by TensorBundle checkpoints, TFRecord files
  * and TensorBoard event files (the reference gets these from TensorFlow's runtime).
