@@ -780,8 +780,8 @@ int launch_variant(int epi, int grid, int threads, int smem_bytes, cudaStream_t 
       case 1: return launch_instance<KC, BN, PRE, TWO, 1>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
       default: break;
     }
+    if (epi == 3) return launch_instance<KC, BN, PRE, TWO, 3>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
     if constexpr (!PRE) {
-      if (epi == 3) return launch_instance<KC, BN, PRE, TWO, 3>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
       if (epi == 5) return launch_instance<KC, BN, PRE, TWO, 5>(grid, threads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
     }
   }

@@ -41,6 +41,9 @@ WGRAD_SIDE_STREAM = os.environ.get("DRN_WGRAD_STREAM", "1") != "0"
 FUSE_BN0 = os.environ.get("DRN_FUSE_BN0", "1") != "0"
 # data gradient of the strided 3x3 convolutions as four parity-phase convolutions (no zero insertion)
 DGRAD_S2_PHASES = os.environ.get("DRN_DGRAD_S2", "1") != "0"
+# timing experiments only (results are wrong): leave out a class of kernels to see what the step would
+# gain if it were free - "wgrad", "bnbwd", "bnfwd", comma separated
+_DEBUG_SKIP = frozenset(filter(None, os.environ.get("DRN_DEBUG_SKIP", "").split(",")))
 
 
 def _fuse_bn0(blk: BlockSpec) -> bool:
@@ -53,6 +56,15 @@ def _fuse_bn0(blk: BlockSpec) -> bool:
     if blk.cin not in (256, 512, 1024) or blk.cin > int(os.environ.get("DRN_FUSE_BN0_MAXC", "512")):
         return False
     return blk.proj is None or blk.cin == 256
+
+
+def _fuse_bn_last(blk: BlockSpec) -> bool:
+    """The BatchNorm+ReLU in front of a bottleneck block's LAST (1x1) convolution applied by that
+    convolution's prologue (and by its filter gradient's) to the raw output of the 3x3 convolution,
+    so that activation is never stored.  DRN_FUSE_BN2 = largest channel count to fuse (0 = off)."""
+    c = blk.convs[-1]
+    maxc = int(os.environ.get("DRN_FUSE_BN2", "0"))
+    return len(blk.convs) == 3 and c.ksize == 1 and c.stride == 1 and c.cin % 64 == 0 and c.cin <= maxc
 
 
 def _fuse_bnbwd(blk: BlockSpec) -> bool:
@@ -396,6 +408,7 @@ class NativeResNet:
         d["bn0"] = _BN(blk.bns[0], self)
         d["fuse"] = _fuse_bn0(blk)
         d["fuse_bwd"] = _fuse_bnbwd(blk)
+        d["fuse_last"] = _fuse_bn_last(blk)
         d["a0"] = None if d["fuse"] else self._act(B, blk.hin, blk.hin, blk.cin)
         sizes = [B * blk.hin * blk.hin * blk.cin]
         if blk.proj is not None:
@@ -413,7 +426,8 @@ class NativeResNet:
             sizes.append(y.numel())
             if not last:
                 bns.append(_BN(blk.bns[i + 1], self))
-                acts.append(self._act(B, c.hout, c.hout, c.cout))
+                fused = d["fuse_last"] and i + 2 == len(blk.convs)    # consumed raw by the last convolution
+                acts.append(None if fused else self._act(B, c.hout, c.hout, c.cout))
         d.update(convs=convs, bns=bns, ys=ys, acts=acts, max_elems=max(sizes))
         return d
 
@@ -567,6 +581,8 @@ class NativeResNet:
             self._wg_last = None
 
     def _wgrad(self, conv: _Conv, x, dy, dy_idx: Optional[int] = None, pre=None):
+        if "wgrad" in _DEBUG_SKIP:
+            return
         if pre is not None:
             self._on_wgrad_stream(lambda st: _nl.call("drn_conv_wgrad_pre", ctypes.byref(conv.desc), _p(x), _p(pre),
                                                       _p(dy), _p(conv.dw), 0, st), dy_idx)
@@ -587,6 +603,8 @@ class NativeResNet:
     def _bn_fwd(self, bn: _BN, y, out, training: bool, relu: bool = True):
         """a = relu(bn(y)): statistics -> scale/shift -> apply, one launch in training mode."""
         count = y.numel() // bn.C
+        if "bnfwd" in _DEBUG_SKIP:
+            return
         if training:
             _nl.call("drn_bn_finalize_apply", _p(y), _p(bn.fstats), bn.fstats.stride(0), count, _p(bn.gamma),
                      _p(bn.beta), _p(bn.run_mean), _p(bn.run_var), BN_DECAY, BN_EPS, _p(bn.ss), _p(bn.mi),
@@ -665,18 +683,23 @@ class NativeResNet:
             self._conv(pj.desc, h, pj.w, b["shortcut"], pre=pre, pull=self._pull(pj.spec.name))
             shortcut = b["shortcut"]
         convs = b["convs"]
+        pre_last = None
         for i, c in enumerate(convs):
             last = i + 1 == len(convs)
             y = b["ys"][i]
             if last:
-                self._conv(c.desc, h, c.w, y, side=shortcut, mode=EPI_RESADD,
+                self._conv(c.desc, h, c.w, y, side=shortcut, mode=EPI_RESADD, pre=pre_last,
                            stats=next_bn.fstats if training else None, pull=self._pull(c.spec.name))
             else:
                 bn = b["bns"][i]
                 self._conv(c.desc, h, c.w, y, stats=bn.fstats if training else None, pre=pre if i == 0 else None,
                            pull=self._pull(c.spec.name))
-                self._bn_fwd(bn, y, b["acts"][i], training)
-                h = b["acts"][i]
+                if b.get("fuse_last") and i + 2 == len(convs):
+                    self._bn_finalize(bn, y.numel() // bn.C, training)
+                    h, pre_last = y, bn.ss
+                else:
+                    self._bn_fwd(bn, y, b["acts"][i], training)
+                    h = b["acts"][i]
         return b["ys"][-1]
 
     # ---- loss ---------------------------------------------------------------------------------
@@ -796,6 +819,8 @@ class NativeResNet:
                  _p(bn.dgamma), _p(bn.dbeta), _p(bn.coef), bn.C, self._st())
 
     def _bn_bwd(self, bn: _BN, dm, y, addend, out):
+        if "bnbwd" in _DEBUG_SKIP:
+            return
         st = self._st()
         count = y.numel() // bn.C
         _nl.call("drn_bn_bwd_finalize_apply", _p(dm), _p(y), _p(bn.bstats), bn.bstats.stride(0), count,
@@ -811,7 +836,10 @@ class NativeResNet:
         for i in range(len(convs) - 1, 0, -1):
             c, bn = convs[i], bns[i - 1]
             y_prev, a_prev = ys[i - 1], acts[i - 1]
-            self._wgrad(c, a_prev, dy, dy_i)
+            if a_prev is None:      # fuse_last: the filter gradient rebuilds relu(bn(y_prev)) itself
+                self._wgrad(c, y_prev, dy, dy_i, pre=bn.ss)
+            else:
+                self._wgrad(c, a_prev, dy, dy_i)
             dm_i, dm = self._get(y_prev)
             if c.wd_s2 is not None:
                 # strided 3x3: four parity-phase convolutions over dy, interleaved by the mask kernel
