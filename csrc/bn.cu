@@ -145,9 +145,11 @@ __global__ void bn_apply_kernel(const BF8* __restrict__ y, const float2* __restr
   }
 }
 
-// per-channel sum and sum of squares of a [M][C] tensor (standalone producer of BN statistics)
-__global__ void bn_stats_kernel(const BF8* __restrict__ y, float* __restrict__ stats, int stats_ld,
-                                long long M, int c8) {
+// per-channel sum and sum of squares of a [M][C] tensor (standalone producer of BN statistics);
+// with a second tensor y2: (sum y, sum y*y2) - the two reductions of a BatchNorm backward from the
+// masked gradient and the BatchNorm input.  det: ticket of the deterministic mode (common.cuh) or nullptr.
+__global__ void bn_stats_kernel(const BF8* __restrict__ y, const BF8* __restrict__ y2, float* __restrict__ stats,
+                                int stats_ld, long long M, int c8, unsigned int* det) {
   pdl_trigger();
   pdl_wait();
   __shared__ float s_acc[kThreads * 16];
@@ -158,12 +160,13 @@ __global__ void bn_stats_kernel(const BF8* __restrict__ y, float* __restrict__ s
 #pragma unroll
   for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
   for (long long m = (long long)blockIdx.x * lanes + pl; m < M; m += (long long)gridDim.x * lanes) {
-    float f[8];
+    float f[8], f2[8];
     unpack8(y[m * c8 + cg], f);
+    if (y2 != nullptr) unpack8(y2[m * c8 + cg], f2);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       s1[k] += f[k];
-      s2[k] = fmaf(f[k], f[k], s2[k]);
+      s2[k] = fmaf(f[k], y2 != nullptr ? f2[k] : f[k], s2[k]);
     }
   }
 #pragma unroll
@@ -172,6 +175,7 @@ __global__ void bn_stats_kernel(const BF8* __restrict__ y, float* __restrict__ s
     s_acc[threadIdx.x * 16 + 8 + k] = s2[k];
   }
   __syncthreads();
+  det_turn_begin(det, blockIdx.x);
   // thread t < c8*16 reduces one (channel, which) pair over the pixel lanes
   for (int t = threadIdx.x; t < c8 * 16; t += blockDim.x) {
     const int g = t / 16, k = t % 16;
@@ -180,6 +184,7 @@ __global__ void bn_stats_kernel(const BF8* __restrict__ y, float* __restrict__ s
     const int ch = g * 8 + (k & 7);
     atomicAdd(stats + (k >> 3) * stats_ld + ch, a);
   }
+  det_turn_end(det, blockIdx.x + 1 == gridDim.x ? 0u : blockIdx.x + 1);
 }
 
 // dm = (da [+ addend]) * [y*scale+shift > 0];  stats += (sum dm, sum dm*y).
@@ -192,7 +197,7 @@ __global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8*
                                           float bcast_scale, const BF8* __restrict__ y,
                                           const float2* __restrict__ scale_shift,
                                           BF8* __restrict__ dm, float* __restrict__ stats,
-                                          int stats_ld, long long M, int c8) {
+                                          int stats_ld, long long M, int c8, unsigned int* det) {
   pdl_trigger();
   pdl_wait();
   __shared__ float s_acc[kThreads * 16];
@@ -285,12 +290,14 @@ __global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8*
     s_acc[threadIdx.x * 16 + 8 + k] = s2[k];
   }
   __syncthreads();
+  det_turn_begin(det, blockIdx.x);
   for (int t = threadIdx.x; t < c8 * 16; t += blockDim.x) {
     const int g = t / 16, k = t % 16;
     float a = 0.f;
     for (int l = 0; l < lanes; ++l) a += s_acc[(l * c8 + g) * 16 + k];
     atomicAdd(stats + (k >> 3) * stats_ld + g * 8 + (k & 7), a);
   }
+  det_turn_end(det, blockIdx.x + 1 == gridDim.x ? 0u : blockIdx.x + 1);
 }
 
 // Post-activation (v1) blocks: out = relu(bn(y) + shortcut).  Backward of the ReLU plus the two
@@ -300,7 +307,8 @@ __global__ void bn_bwd_mask_reduce_kernel(const BF8* __restrict__ da, const BF8*
 __global__ void relu_bwd_reduce_kernel(const BF8* __restrict__ g, const BF8* __restrict__ out,
                                        const BF8* __restrict__ y, const BF8* __restrict__ y2,
                                        BF8* __restrict__ dm, float* __restrict__ stats,
-                                       float* __restrict__ stats2, int stats_ld, long long M, int c8) {
+                                       float* __restrict__ stats2, int stats_ld, long long M, int c8,
+                                       unsigned int* det) {
   pdl_trigger();
   pdl_wait();
   __shared__ float s_acc[kThreads * 24];
@@ -343,6 +351,7 @@ __global__ void relu_bwd_reduce_kernel(const BF8* __restrict__ g, const BF8* __r
     s_acc[threadIdx.x * 24 + 16 + k] = s3[k];
   }
   __syncthreads();
+  det_turn_begin(det, blockIdx.x);
   for (int t = threadIdx.x; t < c8 * 24; t += blockDim.x) {
     const int grp = t / 24, k = t % 24;
     float a = 0.f;
@@ -357,6 +366,7 @@ __global__ void relu_bwd_reduce_kernel(const BF8* __restrict__ g, const BF8* __r
       atomicAdd(stats2 + stats_ld + c, a);
     }
   }
+  det_turn_end(det, blockIdx.x + 1 == gridDim.x ? 0u : blockIdx.x + 1);
 }
 
 // dgamma, dbeta and the coefficients of dy = A*dm + B*y + C
@@ -702,16 +712,30 @@ extern "C" int drn_bn_apply(const void* y, const void* scale_shift, const void* 
   return 0;
 }
 
+// grid of the reduction kernels: in the deterministic mode one resident block per SM (the blocks
+// take turns in index order)
+static int reduce_grid(long long M, int C, int per_sm) {
+  const int lanes = kThreads / (C / 8);
+  long long blocks = (M + lanes - 1) / lanes;
+  const long long cap = (long long)num_sms() * (deterministic() ? 1 : per_sm);
+  return (int)(blocks > cap ? cap : blocks);
+}
+
 extern "C" int drn_bn_stats(const void* y, float* stats, int stats_ld, long long M, int C,
                             void* stream) {
   if (int e = check_c(C, "bn_stats")) return e;
-  const int lanes = kThreads / (C / 8);
-  long long blocks = (M + lanes - 1) / lanes;
-  const long long cap = (long long)num_sms() * 4;
-  if (blocks > cap) blocks = cap;
-  DRN_CHECK_CUDA(launch_pdl(bn_stats_kernel, dim3((int)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
-                            (const BF8*)y, stats,
-                                                                      stats_ld, M, C / 8));
+  DRN_CHECK_CUDA(launch_pdl(bn_stats_kernel, dim3(reduce_grid(M, C, 4)), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)y, (const BF8*)nullptr, stats, stats_ld, M, C / 8, det_ticket(kDetBnStats)));
+  return 0;
+}
+
+// stats[0][c] += sum_m a[m][c];  stats[1][c] += sum_m a[m][c] * y[m][c]
+extern "C" int drn_bn_pair_reduce(const void* a, const void* y, float* stats, int stats_ld, long long M, int C,
+                                  void* stream) {
+  if (int e = check_c(C, "bn_pair_reduce")) return e;
+  DRN_REQUIRE(a != nullptr && y != nullptr, "bn_pair_reduce: two tensors needed");
+  DRN_CHECK_CUDA(launch_pdl(bn_stats_kernel, dim3(reduce_grid(M, C, 4)), dim3(kThreads), 0, (cudaStream_t)stream,
+                            (const BF8*)a, (const BF8*)y, stats, stats_ld, M, C / 8, det_ticket(kDetPairReduce)));
   return 0;
 }
 
@@ -727,10 +751,7 @@ extern "C" int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int ad
   DRN_REQUIRE(da != nullptr || addend_kind != 0, "bn_bwd_mask_reduce: no gradient given");
   const long long M = (long long)N * H * W;
   DRN_REQUIRE(M < (1LL << 31), "bn_bwd_mask_reduce: more than 2^31 pixels");
-  const int lanes = kThreads / (C / 8);
-  long long blocks = (M + lanes - 1) / lanes;
-  const long long cap = (long long)num_sms() * 8;
-  if (blocks > cap) blocks = cap;
+  const int blocks = reduce_grid(M, C, 8);
   auto kern = addend_kind == 0   ? bn_bwd_mask_reduce_kernel<0>
               : addend_kind == 1 ? bn_bwd_mask_reduce_kernel<1>
               : addend_kind == 2 ? bn_bwd_mask_reduce_kernel<2>
@@ -738,7 +759,8 @@ extern "C" int drn_bn_bwd_mask_reduce(const void* da, const void* addend, int ad
                                  : bn_bwd_mask_reduce_kernel<4>;
   DRN_CHECK_CUDA(launch_pdl(kern, dim3((int)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
                             (const BF8*)da, (const BF8*)addend, H, W, Ha, Wa, bcast_scale, (const BF8*)y,
-                            (const float2*)scale_shift, (BF8*)dm, stats, stats_ld, M, C / 8));
+                            (const float2*)scale_shift, (BF8*)dm, stats, stats_ld, M, C / 8,
+                            det_ticket(kDetMaskReduce)));
   return 0;
 }
 
@@ -748,13 +770,10 @@ extern "C" int drn_relu_bwd_reduce(const void* g, const void* out, const void* y
                                    int C, void* stream) {
   if (int e = check_c(C, "relu_bwd_reduce")) return e;
   DRN_REQUIRE((y2 == nullptr) == (stats2 == nullptr), "relu_bwd_reduce: y2 and stats2 go together");
-  const int lanes = kThreads / (C / 8);
-  long long blocks = (M + lanes - 1) / lanes;
-  const long long cap = (long long)num_sms() * 8;
-  if (blocks > cap) blocks = cap;
+  const int blocks = reduce_grid(M, C, 8);
   DRN_CHECK_CUDA(launch_pdl(relu_bwd_reduce_kernel, dim3((int)blocks), dim3(kThreads), 0, (cudaStream_t)stream,
                             (const BF8*)g, (const BF8*)out, (const BF8*)y, (const BF8*)y2, (BF8*)dm, stats,
-                            stats2, stats_ld, M, C / 8));
+                            stats2, stats_ld, M, C / 8, det_ticket(kDetReluBwd)));
   return 0;
 }
 

@@ -34,6 +34,28 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   return t;
 }
 
+// ----------------------------------------------------------------------------------------------
+// Deterministic mode (drn_set_deterministic): kernels that add per-block partial sums into global
+// memory with floating-point atomics take turns in block-index order instead, so the order of the
+// additions - and with it every bit of the result - is the same from run to run.  A launcher passes
+// a ticket word (0 before the launch, reset to 0 by the last block) or nullptr for the normal mode.
+// Waiting for block b-1 is safe: the hardware dispatches blocks in index order, so b-1 is resident
+// or finished whenever b runs.
+// ----------------------------------------------------------------------------------------------
+constexpr int kDetFamilies = 16;       // one ticket per kernel family that may run concurrently
+constexpr int kDetWgradUnits = 1024;   // split-K semaphores of the filter gradient, one per output tile
+enum DetFamily { kDetBnStats = 0, kDetMaskReduce, kDetReluBwd, kDetPairReduce, kDetLoss, kDetOptim };
+extern __device__ unsigned int g_det_tickets[kDetFamilies + kDetWgradUnits];
+
+__device__ __forceinline__ unsigned int det_ld_acquire(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void det_st_release(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
@@ -90,6 +112,27 @@ static __device__ __noinline__ void watchdog_fire(uint32_t code) {
   __threadfence_system();
   __trap();
 }
+// Ordered section of a whole thread block (every thread calls both; no-ops when ticket == nullptr):
+// global atomics issued between begin and end happen after those of all lower-numbered blocks.
+__device__ __forceinline__ void det_turn_begin(unsigned int* ticket, unsigned int turn) {
+  if (ticket == nullptr) return;
+  if (threadIdx.x == 0) {
+    const uint64_t t0 = globaltimer_ns();
+    uint32_t it = 0;
+    while (det_ld_acquire(ticket) != turn) {
+      __nanosleep(64);
+      if (((++it) & 0x3ff) == 0 && globaltimer_ns() - t0 > DRN_WATCHDOG_NS) watchdog_fire(0x90);
+    }
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void det_turn_end(unsigned int* ticket, unsigned int next) {
+  if (ticket == nullptr) return;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) det_st_release(ticket, next);
+}
+
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, uint32_t code = 1) {
   if (mbar_try_wait(bar, parity)) return;
   uint64_t t0 = globaltimer_ns();

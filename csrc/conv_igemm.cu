@@ -938,6 +938,18 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
               "conv_igemm: the BNBWD modes need bn_scale_shift");
   DRN_REQUIRE(mode != DRN_EPI_BNBWD_APPLY || stats == nullptr, "conv_igemm: BNBWD_APPLY takes no statistics");
   DRN_REQUIRE(stats == nullptr || stats_ld >= d.K, "conv_igemm: stats_ld < K");
+  if (stats != nullptr && deterministic()) {
+    // Deterministic mode: the epilogue adds its per-channel sums with float atomics in whatever order
+    // the CTAs finish.  Run the convolution without them and take the sums of what it stored in an
+    // ordered pass (thread-local prologue / view / pull / two-side settings stay in force for the call).
+    DRN_REQUIRE(y != nullptr && mode != DRN_EPI_BNBWD_APPLY,
+                "conv_igemm: statistics-only launches are not available in the deterministic mode");
+    if (int rc = drn_conv_igemm(desc, x, w, y, side, nullptr, 0, bn_scale_shift, mode, force_bn, stream)) return rc;
+    const long long M = 1LL * d.N * d.P * d.Q;
+    if (mode == DRN_EPI_BNBWD || mode == DRN_EPI_BNBWD_ADD)   // (sum dm, sum dm * BatchNorm input)
+      return drn_bn_pair_reduce(y, side, stats, stats_ld, M, d.K, stream);
+    return drn_bn_stats(y, stats, stats_ld, M, d.K, stream);
+  }
   int bn = force_bn;
   if (bn == 0) {
     // Measured on B200 over every ResNet-50 role (bench/tune_igemm.py): a 256-wide tile costs about

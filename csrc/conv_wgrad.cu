@@ -40,6 +40,7 @@ struct WgradParams {
   int Kout, C;
   float* dw;
   const float2* pre_ss;  // PRE: (scale, shift) per input channel, X is the RAW tensor
+  unsigned int* det_sem; // deterministic mode: one semaphore per (Cout tile, column tile), else nullptr
 };
 
 template <int CWA, int CWB>
@@ -276,6 +277,19 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
       const int co = co_tile * 128 + row;
       mbar_wait(tfull_bar, 0, 0x140);
       tc_fence_after();
+      // deterministic mode: the split-K partial tiles of one output tile are added in split order
+      unsigned int* sem = (p.det_sem != nullptr && p.splits > 1) ? p.det_sem + blockIdx.x / p.splits : nullptr;
+      if (sem != nullptr) {
+        if (threadIdx.x == 64) {
+          const uint64_t t0 = globaltimer_ns();
+          uint32_t it = 0;
+          while (det_ld_acquire(sem) != (unsigned)split) {
+            __nanosleep(64);
+            if (((++it) & 0x3ff) == 0 && globaltimer_ns() - t0 > DRN_WATCHDOG_NS) watchdog_fire(0x148);
+          }
+        }
+        named_bar_sync(1, 128);
+      }
       float* dst_row = p.dw + (long long)co * p.cols_total + n0;
 #pragma unroll 1
       for (int c0 = 0; c0 < ncols; c0 += 16) {
@@ -290,7 +304,17 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
                        __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
         }
       }
+      if (sem != nullptr) {
+        __threadfence();
+        named_bar_sync(1, 128);
+        if (threadIdx.x == 64) det_st_release(sem, split + 1 == p.splits ? 0u : (unsigned)(split + 1));
+      }
     }
+  } else if (p.det_sem != nullptr && p.splits > 1 && threadIdx.x == 64) {
+    // a trailing split without pixels still takes (and passes on) its turn
+    unsigned int* sem = p.det_sem + blockIdx.x / p.splits;
+    while (det_ld_acquire(sem) != (unsigned)split) __nanosleep(64);
+    det_st_release(sem, split + 1 == p.splits ? 0u : (unsigned)(split + 1));
   }
 
   tc_fence_before();
@@ -334,6 +358,8 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
     if (splits < 1) splits = 1;
   }
   if (splits > p.chunks_total) splits = p.chunks_total;
+  p.det_sem = det_ticket(kDetFamilies);
+  if (p.det_sem != nullptr && units > kDetWgradUnits) splits = 1;
   p.splits = splits;
   p.chunks_per_split = (p.chunks_total + splits - 1) / splits;
   p.S = d.S;

@@ -10,6 +10,30 @@ namespace drn {
 __device__ unsigned int g_watchdog_flag = 0;
 __device__ unsigned int* g_watchdog_host = nullptr;
 static unsigned int* g_mailbox[64] = {};   // host side of the per-device mailbox
+__device__ unsigned int g_det_tickets[kDetFamilies + kDetWgradUnits] = {};
+static int g_deterministic = -1;           // drn_set_deterministic(); -1 = DRN_DETERMINISTIC / off
+
+bool deterministic() {
+  if (g_deterministic >= 0) return g_deterministic != 0;
+  static const bool env = []() {
+    const char* e = getenv("DRN_DETERMINISTIC");
+    return e != nullptr && atoi(e) != 0;
+  }();
+  return env;
+}
+
+unsigned int* det_ticket(int index) {
+  if (!deterministic()) return nullptr;
+  static unsigned int* base[64] = {};
+  const int dev = current_device();
+  if (dev < 0 || dev >= 64) return nullptr;
+  if (base[dev] == nullptr) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, g_det_tickets) != cudaSuccess) return nullptr;
+    base[dev] = static_cast<unsigned int*>(p);
+  }
+  return base[dev] + index;
+}
 
 std::string& last_error() {
   static thread_local std::string s;
@@ -230,5 +254,16 @@ int drn_set_pdl_mask(int mask) {
   drn::g_pdl_override = mask;
   return 0;
 }
+
+// Deterministic mode: 1 = every floating-point accumulation across thread blocks happens in a fixed
+// order (bit-identical results from run to run, slower), 0 = off, -1 = back to DRN_DETERMINISTIC.
+// Convolutions then take their BatchNorm statistics in a separate ordered pass instead of in the
+// epilogue, the filter gradient reduces its split-K partial tiles in split order, the BatchNorm /
+// loss / optimizer reductions take turns block by block.
+int drn_set_deterministic(int on) {
+  drn::g_deterministic = on;
+  return 0;
+}
+int drn_deterministic() { return drn::deterministic() ? 1 : 0; }
 
 }  // extern "C"

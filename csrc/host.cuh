@@ -124,4 +124,9 @@ const void*& current_pull();
 // conv_igemm.cu Epi2.
 const void*& current_epi2();
 
+// Deterministic mode (drn_set_deterministic / DRN_DETERMINISTIC=1) and the device address of ticket
+// word `index` of common.cuh's g_det_tickets on the current device (nullptr when the mode is off).
+bool deterministic();
+unsigned int* det_ticket(int index);
+
 }  // namespace drn

@@ -33,7 +33,7 @@ __global__ void softmax_xent_kernel(const __nv_bfloat16* __restrict__ logits, in
                                     const float* __restrict__ bias, const int* __restrict__ labels,
                                     int classes, float grad_scale, __nv_bfloat16* __restrict__ dlogits,
                                     float* __restrict__ dbias, float* __restrict__ probs,
-                                    float* __restrict__ loss_sum, int* __restrict__ correct) {
+                                    float* __restrict__ loss_sum, int* __restrict__ correct, unsigned int* det) {
   pdl_trigger();
   pdl_wait();
   __shared__ float s_red[kThreads / 32];
@@ -70,6 +70,7 @@ __global__ void softmax_xent_kernel(const __nv_bfloat16* __restrict__ logits, in
   const float sum = block_reduce(se, s_red, false);
   const float inv = 1.f / sum;
 
+  det_turn_begin(det, blockIdx.x);    // deterministic mode: the rows add their loss / dbias terms in order
   if (threadIdx.x == 0) {
     const float zl = __bfloat162float(z[label]) + (bias ? bias[label] : 0.f);
     atomicAdd(loss_sum, (__logf(sum) + gmax - zl));
@@ -86,6 +87,7 @@ __global__ void softmax_xent_kernel(const __nv_bfloat16* __restrict__ logits, in
     }
     if (dlogits) dlogits[(long long)row * ld + j] = __float2bfloat16(g);
   }
+  det_turn_end(det, blockIdx.x + 1 == gridDim.x ? 0u : blockIdx.x + 1);
 }
 
 }  // namespace
@@ -103,6 +105,6 @@ extern "C" int drn_softmax_xent(const void* logits, int ld, const float* bias, c
   DRN_REQUIRE(classes <= ld, "softmax_xent: classes (%d) > ld (%d)", classes, ld);
   DRN_CHECK_CUDA(launch_pdl(softmax_xent_kernel, dim3(B), dim3(kThreads), 0, (cudaStream_t)stream,
                             (const __nv_bfloat16*)logits, ld, bias, labels, classes, grad_scale, (__nv_bfloat16*)dlogits,
-      dbias, probs, loss_sum, correct));
+      dbias, probs, loss_sum, correct, det_ticket(kDetLoss)));
   return 0;
 }

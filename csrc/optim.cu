@@ -20,7 +20,7 @@ namespace {
 __global__ void sgd_momentum_kernel(float4* __restrict__ w, float4* __restrict__ g,
                                     float4* __restrict__ m, uint2* __restrict__ shadow,
                                     long long n4, const float* __restrict__ hyper,
-                                    float* __restrict__ l2_sum, int zero_grad) {
+                                    float* __restrict__ l2_sum, int zero_grad, unsigned int* det) {
   pdl_trigger();
   pdl_wait();
   const float lr = hyper[0], mu = hyper[1], wd = hyper[2], gs = hyper[3];
@@ -51,7 +51,14 @@ __global__ void sgd_momentum_kernel(float4* __restrict__ w, float4* __restrict__
     if (threadIdx.x == 0) {
       float t = 0.f;
       for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += s[i];
+      if (det != nullptr) {     // deterministic mode: the blocks add in index order
+        while (det_ld_acquire(det) != blockIdx.x) __nanosleep(64);
+      }
       atomicAdd(l2_sum, t);
+      if (det != nullptr) {
+        __threadfence();
+        det_st_release(det, blockIdx.x + 1 == gridDim.x ? 0u : blockIdx.x + 1);
+      }
     }
   }
 }
@@ -220,9 +227,12 @@ extern "C" int drn_sgd_momentum(float* master, float* grad, float* mom, void* sh
                                 void* stream) {
   DRN_REQUIRE(n % 4 == 0, "sgd_momentum: n must be a multiple of 4");
   const long long n4 = n / 4;
-  DRN_CHECK_CUDA(launch_pdl(sgd_momentum_kernel, dim3(ew_grid(n4, 256)), dim3(256), 0, (cudaStream_t)stream,
+  unsigned int* det = l2_sum != nullptr ? det_ticket(kDetOptim) : nullptr;
+  int grid = ew_grid(n4, 256);
+  if (det != nullptr && grid > 2 * num_sms()) grid = 2 * num_sms();   // the blocks take turns: keep them few
+  DRN_CHECK_CUDA(launch_pdl(sgd_momentum_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream,
                             (float4*)master, (float4*)grad, (float4*)mom, (uint2*)shadow_bf16, n4, hyper, l2_sum,
-      zero_grad));
+                            zero_grad, det));
   return 0;
 }
 

@@ -52,6 +52,8 @@ _SIGNATURES = {
     "drn_watchdog_arm": (_i, []),
     "drn_num_sms": (_i, []),
     "drn_set_pdl_mask": (_i, [_i]),
+    "drn_set_deterministic": (_i, [_i]),
+    "drn_deterministic": (_i, []),
     "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
     "drn_conv_igemm_ex": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, ctypes.POINTER(PullDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
@@ -72,6 +74,7 @@ _SIGNATURES = {
     "drn_bn_inference_params": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _i, _vp]),
     "drn_bn_apply": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp]),
     "drn_bn_stats": (_i, [_vp, _vp, _i, _ll, _i, _vp]),
+    "drn_bn_pair_reduce": (_i, [_vp, _vp, _vp, _i, _ll, _i, _vp]),
     "drn_bn_bwd_mask_reduce": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "drn_relu_bwd_reduce": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _vp]),
     "drn_bn_bwd_finalize": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _vp, _vp, _i, _vp]),

@@ -79,6 +79,7 @@ class TrainConfig:
     input_decode: str = "auto"
     ps_pull: str = "push"
     input_workers: int = 0
+    deterministic: bool = False
 
 
 @dataclass(frozen=True)
@@ -162,7 +163,7 @@ def from_flags(f: FlagValues, entry: str = "train") -> Config:
         allreduce_algo=f.allreduce_algo, max_steps_per_run=f.max_steps_per_run,
         legacy_input=f.legacy_input, synthetic_data=f.synthetic_data, profile=f.profile,
         input_decode=getattr(f, "input_decode", "auto"), ps_pull=getattr(f, "ps_pull", "push"),
-        input_workers=getattr(f, "input_workers", 0))
+        input_workers=getattr(f, "input_workers", 0), deterministic=bool(getattr(f, "deterministic", False)))
     paths = PathConfig(f.train_data_path, f.eval_data_path, f.train_dir, f.eval_dir, f.log_root)
     ev = EvalConfig(f.eval_batch_count, f.eval_once, f.eval_interval_secs,
                     f.batch_size if imagenet else 100)  # CIFAR evaluator: fixed 100 (resnet_cifar_eval.py:87)

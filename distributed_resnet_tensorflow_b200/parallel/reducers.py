@@ -83,8 +83,8 @@ class _ReducerBase:
 
     def use_multicast(self) -> bool:
         """NVLS multimem instructions unless the fabric has no multicast or a *_p2p algorithm was asked for."""
-        if self.algo.endswith("p2p"):
-            return False
+        if self.algo.endswith("p2p") or _nl.load().drn_deterministic():
+            return False      # deterministic mode: peers are read in a fixed rank order
         return bool(self.grad_buf.multicast_ptr)
 
     def algorithm_for(self, nbytes: int) -> str:

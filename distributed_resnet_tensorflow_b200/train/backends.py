@@ -217,9 +217,14 @@ class TorchBackend:
 class NativeBackend:
     def __init__(self, spec: NetSpec, batch: int, ctx: DistContext, device: str = "cuda:0",
                  weight_decay: float = 1e-4, momentum: float = 0.9, seed: int = 0, cifar_pad: int = 4,
-                 use_graph: bool = True, algo: str = "auto", ps_pull: str = "push"):
+                 use_graph: bool = True, algo: str = "auto", ps_pull: str = "push", deterministic: bool = False):
         from ..train.native import NativeTrainer
         self.spec, self.B, self.ctx = spec, batch, ctx
+        if deterministic:
+            # process-wide library switch (include/drn_b200.h: drn_set_deterministic); the reducers
+            # consult it too (peer loads in rank order instead of switch reductions)
+            from .._native import lib as _nl
+            _nl.call("drn_set_deterministic", 1)
         comm = None
         if ctx.distributed:
             from ..parallel import make_reducer

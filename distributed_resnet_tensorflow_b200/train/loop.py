@@ -174,7 +174,8 @@ def build_backend(cfg: Config, spec: NetSpec, ctx: DistContext, backend: str, de
     if backend == "native":
         return NativeBackend(spec, batch, ctx, device=device, weight_decay=t.weight_decay,
                              momentum=t.momentum if t.optimizer == "mom" else 0.0, seed=t.seed,
-                             cifar_pad=pad, use_graph=t.cuda_graph, algo=t.allreduce_algo, ps_pull=t.ps_pull)
+                             cifar_pad=pad, use_graph=t.cuda_graph, algo=t.allreduce_algo, ps_pull=t.ps_pull,
+                             deterministic=t.deterministic)
     dtype = "fp32" if device == "cpu" else t.dtype
     return TorchBackend(spec, batch, ctx, device=device, dtype=dtype, weight_decay=t.weight_decay,
                         momentum=t.momentum if t.optimizer == "mom" else 0.0, seed=t.seed, cifar_pad=pad)

@@ -267,6 +267,9 @@ EXTENSION_FLAGS: List[FlagDef] = [
     _s("ps_pull", "push", "Parameter-server path, how workers get the new weights: push (the shard owner "
        "stores them into every replica) | pull (the first convolution that consumes a layer fetches it from "
        "the owners over NVLink)."),
+    _b("deterministic", False, "Native backend: bit-reproducible steps - every floating-point accumulation "
+       "across thread blocks happens in a fixed order (ordered split-K, ordered BatchNorm / loss reductions, "
+       "peer loads in rank order instead of switch reductions). Slower; for parity runs."),
     _n("max_steps_per_run", 0, "Stop this process after N local steps (testing resume)."),
     _s("init_method", "", "torch.distributed init method; default env:// or file-based for "
        "--job_name launches."),

@@ -33,6 +33,15 @@ int drn_num_sms(void);
  * pooling / optimizer kernels, bit 1 = tcgen05 convolution kernels, -1 = default (off).  Pays for
  * launch-bound steps (CIFAR-sized layers: +4 % steps/s), costs throughput on ImageNet-sized ones. */
 int drn_set_pdl_mask(int mask);
+/* Deterministic mode (reference: none - TensorFlow's GPU reductions are not reproducible either; this
+ * is for parity runs).  on = 1: every floating-point accumulation across thread blocks happens in a
+ * fixed order, so a step is bit-identical from run to run on the same GPU type and grid: convolutions
+ * take their BatchNorm statistics in a separate ordered pass instead of with epilogue atomics, the
+ * filter gradient adds its split-K partial tiles in split order, the BatchNorm / loss / optimizer
+ * reductions take turns block by block.  0 = off, -1 = follow the DRN_DETERMINISTIC environment
+ * variable (default off).  Costs throughput. */
+int drn_set_deterministic(int on);
+int drn_deterministic(void);
 
 /* ---------------------------------------------------------------------------------------------
  * Convolution (reference: tf.layers.conv2d in resnet_model_official.py:80-91; ops K1-K4)
@@ -197,6 +206,9 @@ int drn_bn_bwd_finalize_apply(const void* dm, const void* y, const float* stats,
                               float* dgamma, float* dbeta, const void* addend, void* dy, int C,
                               void* stream);
 int drn_bn_stats(const void* y, float* stats, int stats_ld, long long M, int C, void* stream);
+/* stats[0][c] += sum_m a[m][c];  stats[1][c] += sum_m a[m][c] * y[m][c]  (bf16 [M][C] tensors) */
+int drn_bn_pair_reduce(const void* a, const void* y, float* stats, int stats_ld, long long M, int C,
+                       void* stream);
 /* dm = (da [+ addend]) * [y*scale+shift > 0]; stats += (sum dm, sum dm*y).
  * addend_kind: 0 none, 1 same shape, 2 compact stride-2 tensor [N,Ha,Wa,C] added at even pixels,
  * 3 per-image vector [N][C] times bcast_scale (average-pool gradient; da may then be NULL),

@@ -136,3 +136,21 @@ def test_two_worker_parameter_server_cli_saves_timed_checkpoints(tmp_path, pull)
     assert int(v["global_step"]) == 9000
     prec = float(outs[0].split("step = 9000,")[1].split("precision = ")[1].split(",")[0])
     assert prec > 0.5, outs[0][-800:]
+
+
+def test_deterministic_flag_reproduces_a_run_bit_for_bit(tmp_path):
+    """--deterministic: two training runs from the same seed write identical checkpoints (weights,
+    momentum, moving statistics), through the whole product path - input thread, CUDA graph, side
+    stream for the filter gradients, bucketed optimizer."""
+    from distributed_resnet_tensorflow_b200.ckpt.saver import Saver, latest_checkpoint
+    got = []
+    for run in ("a", "b"):
+        root = str(tmp_path / run)
+        out = _run([os.path.join(ROOT, "resnet_cifar_main.py"), "--resnet_size=14", "--batch_size=64", "--num_gpus=1",
+                    f"--log_root={root}", "--train_steps=40", "--log_every=20", "--base_lr=0.05", "--deterministic"])
+        assert "backend=native" in out and "step = 40" in out
+        got.append(Saver.restore(latest_checkpoint(root)))
+    a, b = got
+    assert a.keys() == b.keys()
+    diff = [k for k in a if not np.array_equal(np.asarray(a[k]), np.asarray(b[k]))]
+    assert not diff, f"{len(diff)} of {len(a)} variables differ, e.g. {diff[:5]}"

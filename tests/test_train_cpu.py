@@ -143,9 +143,10 @@ def test_new_flags_reach_the_config():
     from distributed_resnet_tensorflow_b200 import config as C
     from distributed_resnet_tensorflow_b200.utils import flags as F
     v, _ = F.make_flagset(**F.IMAGENET_MAIN).parse(["--ps_pull=pull", "--input_workers=6", "--allreduce_algo=oneshot_p2p",
-                                                    "--resnet_version=1"])
+                                                    "--resnet_version=1", "--deterministic"])
     cfg = C.from_flags(v)
-    assert cfg.train.ps_pull == "pull" and cfg.train.input_workers == 6
+    assert cfg.train.ps_pull == "pull" and cfg.train.input_workers == 6 and cfg.train.deterministic is True
     assert cfg.train.allreduce_algo == "oneshot_p2p" and cfg.model.resnet_version == 1
     cfg = C.from_flags(F.make_flagset().parse([])[0])
     assert cfg.train.ps_pull == "push" and cfg.train.input_workers == 0 and cfg.train.allreduce_algo == "auto"
+    assert cfg.train.deterministic is False
