@@ -41,6 +41,7 @@ struct WgradParams {
   float* dw;
   const float2* pre_ss;  // PRE: (scale, shift) per input channel, X is the RAW tensor
   unsigned int* det_sem; // deterministic mode: one semaphore per (Cout tile, column tile), else nullptr
+  int debug;             // DRN_WGRAD_DEBUG (timing experiments, wrong results): 1 = no red.global, 2 = no MMA
 };
 
 template <int CWA, int CWB>
@@ -209,7 +210,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
                                                    8 * C_::kRBA, kLayA);
             const uint64_t b_desc = make_smem_desc(b_addr + kk * 16 * C_::kRBB, C_::kBBoxBytes,
                                                    8 * C_::kRBB, kLayB);
-            umma_f16(tmem_base, a_desc, b_desc, idesc, (ch | kk) != 0 ? 1u : 0u);
+            if (!(p.debug & 2)) umma_f16(tmem_base, a_desc, b_desc, idesc, (ch | kk) != 0 ? 1u : 0u);
           }
           umma_commit(empty_bar(stage));
           if (++stage == kStages) {
@@ -297,7 +298,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
         uint32_t v[16];
         tmem_ld_32x16(taddr, v);
         tmem_ld_wait();
-        if (co < p.Kout) {
+        if (co < p.Kout && !(p.debug & 1)) {
 #pragma unroll
           for (int i = 0; i < 16; i += 4)
             red_add_v4(dst_row + c0 + i, __uint_as_float(v[i]), __uint_as_float(v[i + 1]),
@@ -358,6 +359,8 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
     if (splits < 1) splits = 1;
   }
   if (splits > p.chunks_total) splits = p.chunks_total;
+  static const int debug_env = getenv("DRN_WGRAD_DEBUG") ? atoi(getenv("DRN_WGRAD_DEBUG")) : 0;
+  p.debug = debug_env;
   p.det_sem = det_ticket(kDetFamilies);
   if (p.det_sem != nullptr && units > kDetWgradUnits) splits = 1;
   p.splits = splits;
