@@ -165,6 +165,31 @@ def main():
             print(f"allreduce-vs-{mode} max weight diff after one step: {diff:.3e}", flush=True)
         assert diff < 1e-3, ("allreduce vs " + mode + " weights after one step", diff)
 
+    # deterministic mode across replicas: two runs of three steps end in bit-identical weights
+    from distributed_resnet_tensorflow_b200._native import lib as _nl
+    _nl.call("drn_set_deterministic", 1)
+    for mode in ("allreduce", "ps"):
+        finals = []
+        for _ in range(2):
+            if mode == "allreduce":
+                comm = AllreduceReducer(rank, world, dev, provider=provider, algo="auto")
+            else:
+                comm = ParameterServerReducer(rank, world, dev, num_ps=world, provider=provider)
+            assert not comm.use_multicast(), "deterministic mode reads peers in rank order"
+            tr = NativeTrainer(spec, B, device=dev, weight_decay=2e-4, comm=comm, use_graph=True)
+            tr.import_variables(variables)
+            for _ in range(3):
+                tr.train_step(imgs, labs, lr=0.1)
+            torch.cuda.synchronize(); dist.barrier()
+            if mode == "ps":
+                comm.gather_master(tr.engine)
+            finals.append(tr.engine.master.clone())
+            del tr, comm
+        assert torch.equal(finals[0], finals[1]), f"deterministic {mode}: {int((finals[0] != finals[1]).sum())} weights differ"
+        if rank == 0:
+            print(f"deterministic {mode}: two runs of 3 steps bit-identical", flush=True)
+    _nl.call("drn_set_deterministic", -1)
+
     # single-replica reference: mean of the per-replica gradients applied once
     tr1 = NativeTrainer(spec, B, device=dev, weight_decay=2e-4, comm=None, use_graph=False)
     tr1.import_variables(variables)

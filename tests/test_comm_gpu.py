@@ -18,7 +18,7 @@ def _launch(nproc, env_extra=None, port=29611):
            os.path.join(ROOT, "tests", "_comm_worker.py")]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     out = res.stdout + res.stderr
-    sys.stdout.write("\n".join(l for l in out.splitlines() if "allreduce" in l or "steps ok" in l) + "\n")
+    sys.stdout.write("\n".join(l for l in out.splitlines() if "allreduce" in l or "steps ok" in l or "deterministic" in l) + "\n")
     assert res.returncode == 0 and "COMM_WORKER_OK" in out, out[-4000:]
     return out
 
