@@ -805,6 +805,7 @@ extern "C" int drn_bn_finalize_apply(const void* y, const float* stats, int stat
   DRN_REQUIRE(count > 0, "bn_finalize_apply: count must be positive");
   const float unbias = count > 1 ? (float)((double)count / (double)(count - 1)) : 1.f;
   const long long n_vec = count * (C / 8);
+  PdlSmall pdl_small(n_vec);
   DRN_CHECK_CUDA(launch_pdl(bn_finalize_apply_kernel, dim3(fused_grid(n_vec) + 1), dim3(kThreads), 0, (cudaStream_t)stream,
                             (const BF8*)y, stats, stats_ld, (float)(1.0 / (double)count), unbias, gamma, beta, run_mean,
       run_var, 1.f - decay, eps, (float2*)scale_shift, (float2*)mean_invstd, (BF8*)out, n_vec, C / 8,
@@ -821,6 +822,7 @@ extern "C" int drn_bn_bwd_finalize_apply(const void* dm, const void* y, const fl
   const long long n_vec = count * (C / 8);
   static const int variant = getenv("DRN_BN_VARIANT") ? atoi(getenv("DRN_BN_VARIANT")) : 0;
   const int blocks = fused_grid(n_vec) + 1;   // + the publisher block
+  PdlSmall pdl_small(n_vec);
   auto kern = variant == 1   ? bn_bwd_finalize_apply_kernel<2, 1>
               : variant == 2 ? bn_bwd_finalize_apply_kernel<4, 0>
               : variant == 3 ? bn_bwd_finalize_apply_kernel<4, 1>

@@ -763,8 +763,14 @@ int launch_instance(int grid, int threads, int smem_bytes, cudaStream_t stream, 
     DRN_CHECK_CUDA(launch_cluster2(conv_igemm_kernel<KC, BN, PRE, TWO, EPI>, dim3(grid), dim3(threads),
                                    smem_bytes, stream, tA, tB, tC, tR, tR2, p));
   } else {
-    DRN_CHECK_CUDA(launch_pdl_conv(conv_igemm_kernel<KC, BN, PRE, TWO, EPI>, dim3(grid), dim3(threads),
-                                   smem_bytes, stream, tA, tB, tC, tR, tR2, p));
+    // size-based policy (experiment): programmatic dependent launch for layers of at most
+    // DRN_PDL_SMALL_TILES output tiles - launch-bound layers gain from it, large ones lose
+    static const int small_tiles = env_int("DRN_PDL_SMALL_TILES", 0);
+    if (small_tiles > 0 && p.total_tiles <= small_tiles) pdl_override() = 1;
+    const cudaError_t e = launch_pdl_conv(conv_igemm_kernel<KC, BN, PRE, TWO, EPI>, dim3(grid), dim3(threads),
+                                          smem_bytes, stream, tA, tB, tC, tR, tR2, p);
+    pdl_override() = -1;
+    DRN_CHECK_CUDA(e);
   }
   return 0;
 }

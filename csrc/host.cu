@@ -83,6 +83,11 @@ int pdl_mask() {
   return g_pdl_override >= 0 ? g_pdl_override : 0;
 }
 
+int& pdl_override() {
+  static thread_local int v = -1;
+  return v;
+}
+
 int current_device() {
   int dev = -1;
   return cudaGetDevice(&dev) == cudaSuccess ? dev : -1;

@@ -54,6 +54,9 @@ struct PerDeviceOnce {
 // still draining; it must execute pdl_wait() (common.cuh) before touching memory the predecessor
 // produced.  Inside a captured graph this becomes a programmatic edge.  DRN_PDL=0 turns it off.
 int pdl_mask();   // bit 0: element-wise / pooling / optimizer kernels, bit 1: tcgen05 convolution kernels
+// Per-launch override (thread-local, set by a launcher around ONE launch): -1 = follow pdl_mask(),
+// 0 / 1 = without / with the programmatic edge.  Used by the size-based policy (DRN_PDL_SMALL_TILES).
+int& pdl_override();
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl_kind(int kind_bit, void (*kernel)(KArgs...), dim3 grid, dim3 block,
@@ -67,7 +70,8 @@ inline cudaError_t launch_pdl_kind(int kind_bit, void (*kernel)(KArgs...), dim3 
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = (pdl_mask() & kind_bit) ? 1 : 0;
+  const int ov = pdl_override();
+  cfg.numAttrs = (ov >= 0 ? ov != 0 : (pdl_mask() & kind_bit) != 0) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 // Launch with a (2,1,1) thread-block cluster (CTA pairs for tcgen05 cta_group::2).
@@ -88,6 +92,15 @@ inline cudaError_t launch_cluster2(void (*kernel)(KArgs...), dim3 grid, dim3 blo
   cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
+// Scope guard of the size-based policy for element-wise kernels: programmatic edge when the tensor
+// has at most DRN_PDL_SMALL_VECS 16-byte vectors (experiment; 0 = off).
+struct PdlSmall {
+  explicit PdlSmall(long long n_vec) {
+    static const long long lim = getenv("DRN_PDL_SMALL_VECS") ? atoll(getenv("DRN_PDL_SMALL_VECS")) : 0;
+    if (lim > 0 && n_vec <= lim) pdl_override() = 1;
+  }
+  ~PdlSmall() { pdl_override() = -1; }
+};
 #define launch_pdl(...) launch_pdl_kind(1, __VA_ARGS__)
 #define launch_pdl_conv(...) launch_pdl_kind(2, __VA_ARGS__)
 
