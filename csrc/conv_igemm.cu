@@ -37,6 +37,22 @@ constexpr int kNumThreads = 384;    // warp0 TMA (A), warp1 MMA, warp2 TMEM allo
 constexpr int kEpiThreads = 128;
 constexpr int kMaxStages = 8;
 
+// BatchNorm "finalize" of the statistics this convolution accumulates, done by the LAST CTA of the grid
+// to finish (threadfence + counter), so the consumer's scale/shift table exists when the kernel ends and
+// no separate launch is needed between a convolution and the prologue-fused convolution that follows it.
+struct BnFin {
+  unsigned int* counter;   // zero before the launch, reset to zero by the last CTA; nullptr = no finalize
+  float inv_count, unbias, one_minus_decay, eps;
+  const float* gamma;
+  const float* beta;
+  float* run_mean;         // nullable (no moving-average update)
+  float* run_var;
+  float2* scale_shift;     // out [Cout]
+  float2* mean_invstd;     // out [Cout]
+  long long count;         // host side only (deterministic mode runs bn_finalize as its own launch)
+  float decay;
+};
+
 struct ConvParams {
   int m_tiles, n_tiles, total_tiles;
   int k_iters;     // R*S*(C/KC)
@@ -61,16 +77,23 @@ struct ConvParams {
   // the consuming layer applied in shared memory between the TMA load and the MMA)
   const float2* pre_ss;  // [C] (scale, shift)
   long long M;           // valid output rows (rows beyond are forced to zero after the transform)
+  int H_in, W_in;        // input plane (PRE: filter taps that fall into the zero padding stay zero)
   unsigned spin_ns;      // sleep between polls of the non-critical mbarrier waits (0 = spin)
   // PULL: the filter bank is first fetched from the parameter-server shards (peer memory over
   // NVLink) into the local working arena by warp 2 of every CTA, each CTA taking 1/gridDim of it;
   // the weight producer (warp 3) issues its first TMA load only after all CTAs have delivered
   PullArgs pull;         // pull.shadows.p[0] == nullptr: weights are already local
+  BnFin fin;
 };
 constexpr int kPreThreads = 128;    // warps 12-15 of the PRE variant
 
 // second side input / coefficient table of the two-side epilogue modes (thread-local request set by
 // drn_conv_igemm_epi2 around the ordinary launcher)
+const void*& current_bnfin() {
+  static thread_local const void* v = nullptr;
+  return v;
+}
+
 struct Epi2 {
   const void* side2;
   const void* coef;
@@ -334,17 +357,50 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     // per access (512 contiguous bytes, conflict free).  The 128B swizzle stores logical chunk g of
     // row r at physical chunk g ^ (r & 7).
     if constexpr (PRE) {
+      // Thread = (16-byte channel group g of a row, kRows rows): a warp touches whole rows per access
+      // (512 contiguous bytes, conflict free).  The swizzle of a KC*2-byte row (128/64/32 B) stores
+      // logical chunk g of row r at physical chunk g ^ ((r >> kSwzShift) & (kCPR - 1)).
+      constexpr int kCPR = KC / 8;                 // 16-byte chunks per row
+      constexpr int kRows = kCPR;                  // rows per thread: 128 threads cover 128 rows x kCPR chunks
+      constexpr int kRowStep = kPreThreads / kCPR;
+      constexpr int kRB = KC * 2;
+      constexpr int kSwzShift = KC == 64 ? 0 : (KC == 32 ? 1 : 2);
       const int tt = threadIdx.x - kNumThreads;
-      const int g = tt & 7;
-      const int r0 = tt >> 3;  // rows r0 + 16 * i
+      const int g = tt % kCPR;
+      const int r0 = tt / kCPR;  // rows r0 + kRowStep * i
+      uint32_t off[kRows];
+#pragma unroll
+      for (int i = 0; i < kRows; ++i) {
+        const int row = r0 + kRowStep * i;
+        off[i] = row * kRB + ((g ^ ((row >> kSwzShift) & (kCPR - 1))) << 4);
+      }
+      // a filter tap that falls into the zero padding must stay zero after relu(0 * scale + shift):
+      // (input row, input column) of tap (0,0) for each of my rows, per tile; 1x1 layers without
+      // padding only have the rows beyond M to blank
+      const bool taps = p.k_iters != p.c_blocks || p.pad_h != 0 || p.pad_w != 0;
       int stage = 0;
       uint32_t phase = 0;
       for (int t = t_begin; t < t_end; ++t) {
         const int n_tile = t / p.m_tiles;
         const int m_tile = t - n_tile * p.m_tiles;
         const long long m0 = (long long)m_tile * kBM;
+        const bool ragged = m0 + kBM > p.M;   // only the last row tile has rows to blank
+        int ih0[kRows], iw0[kRows];
+#pragma unroll
+        for (int i = 0; i < kRows; ++i) {
+          const long long m = m0 + r0 + kRowStep * i;
+          ih0[i] = iw0[i] = 0;
+          if (m >= p.M) {
+            ih0[i] = -(1 << 28);                 // never valid
+          } else if (taps) {
+            const int rem = (int)(m % p.PQ);
+            const int op = rem / p.Q;
+            ih0[i] = op * p.stride_h - p.pad_h;
+            iw0[i] = (rem - op * p.Q) * p.stride_w - p.pad_w;
+          }
+        }
+        int cb = 0, fr = 0, fs = 0;
         for (int it = 0; it < p.k_iters; ++it) {
-          const int cb = it;   // 1x1 only: the k-step IS the channel block
           const float4* sp = reinterpret_cast<const float4*>(p.pre_ss + cb * KC + g * 8);
           float4 q[4];
 #pragma unroll
@@ -353,33 +409,36 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
           const uint32_t a_addr = sStages + stage * C_::kStageBytes;
           // all loads first, then all arithmetic, then all stores: one warp per scheduler has to
           // find its instruction-level parallelism inside its own stream
-          uint4 v[kBM / 16];
+          uint4 v[kRows];
 #pragma unroll
-          for (int i = 0; i < kBM / 16; ++i) {
-            const int row = r0 + 16 * i;
-            v[i] = ld_shared_v4(a_addr + row * 128 + ((g ^ (row & 7)) << 4));
-          }
-          const bool ragged = m0 + kBM > p.M;   // only the last row tile has rows to blank
+          for (int i = 0; i < kRows; ++i) v[i] = ld_shared_v4(a_addr + off[i]);
 #pragma unroll
-          for (int i = 0; i < kBM / 16; ++i) {
+          for (int i = 0; i < kRows; ++i) {
             uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
 #pragma unroll
             for (int k = 0; k < 4; ++k)   // fp32 fma, then ONE convert-with-ReLU packs both halves
               w[k] = pack_relu_bf16x2(fmaf(bf16lo(w[k]), q[k].x, q[k].y), fmaf(bf16hi(w[k]), q[k].z, q[k].w));
-            if (ragged && m0 + r0 + 16 * i >= p.M) w[0] = w[1] = w[2] = w[3] = 0u;
+            const bool dead = (taps || ragged) &&
+                              (static_cast<unsigned>(ih0[i] + fr) >= static_cast<unsigned>(p.H_in) ||
+                               static_cast<unsigned>(iw0[i] + fs) >= static_cast<unsigned>(p.W_in));
+            if (dead) w[0] = w[1] = w[2] = w[3] = 0u;
             v[i] = make_uint4(w[0], w[1], w[2], w[3]);
           }
 #pragma unroll
-          for (int i = 0; i < kBM / 16; ++i) {
-            const int row = r0 + 16 * i;
-            st_shared_v4(a_addr + row * 128 + ((g ^ (row & 7)) << 4), v[i].x, v[i].y, v[i].z, v[i].w);
-          }
+          for (int i = 0; i < kRows; ++i) st_shared_v4(a_addr + off[i], v[i].x, v[i].y, v[i].z, v[i].w);
           fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's reads
           __syncwarp();
           if (lane == 0) mbar_arrive(ready_bar(stage));   // one arrival per warp
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
+          }
+          if (++cb == p.c_blocks) {   // k-steps run over (filter row, filter column, channel block)
+            cb = 0;
+            if (++fs == p.S) {
+              fs = 0;
+              ++fr;
+            }
           }
         }
       }
@@ -735,6 +794,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     if (leader) tma_store_wait_read<0>();
   }
 
+  if (p.fin.counter != nullptr) __threadfence();   // my statistics (red.global) before the CTA says "done"
   tc_fence_before();
   if (TWO) cluster_sync_all();   // the leader's MMAs read the peer's shared memory until the very end
   else __syncthreads();
@@ -742,6 +802,33 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     tc_fence_after();
     if (TWO) tmem_dealloc_2cta(tmem_base, C_::kTmemCols);
     else tmem_dealloc(tmem_base, C_::kTmemCols);
+  }
+  if (p.fin.counter != nullptr) {
+    // the last CTA to get here sees every CTA's sums: it turns them into the consumer's tables
+    // (same arithmetic as bn_finalize_kernel in bn.cu)
+    __shared__ unsigned int s_last;
+    if (threadIdx.x == 0) {
+      __threadfence();
+      s_last = atomicAdd(p.fin.counter, 1u) == gridDim.x - 1 ? 1u : 0u;
+    }
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      for (int c = threadIdx.x; c < p.n_valid; c += blockDim.x) {
+        const float mean = __ldcg(p.stats + c) * p.fin.inv_count;
+        float var = fmaf(-mean, mean, __ldcg(p.stats + p.stats_ld + c) * p.fin.inv_count);
+        var = fmaxf(var, 0.f);
+        const float invstd = rsqrtf(var + p.fin.eps);
+        const float sc = p.fin.gamma[c] * invstd;
+        p.fin.scale_shift[c] = make_float2(sc, fmaf(-mean, sc, p.fin.beta[c]));
+        p.fin.mean_invstd[c] = make_float2(mean, invstd);
+        if (p.fin.run_mean != nullptr) {
+          p.fin.run_mean[c] -= (p.fin.run_mean[c] - mean) * p.fin.one_minus_decay;
+          p.fin.run_var[c] -= (p.fin.run_var[c] - var * p.fin.unbias) * p.fin.one_minus_decay;
+        }
+      }
+      if (threadIdx.x == 0) *p.fin.counter = 0u;
+    }
   }
 }
 
@@ -883,6 +970,10 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
   if (sm_cap <= 0 || sm_cap > num_sms()) sm_cap = num_sms();
   int grid = p.total_tiles < sm_cap ? p.total_tiles : sm_cap;
   p.pre_ss = reinterpret_cast<const float2*>(current_pre());
+  p.H_in = d.H;
+  p.W_in = d.W;
+  if (current_bnfin() != nullptr && stats != nullptr) p.fin = *static_cast<const BnFin*>(current_bnfin());
+  else memset(&p.fin, 0, sizeof(p.fin));
   if (current_pull() != nullptr) p.pull = *static_cast<const PullArgs*>(current_pull());
   else memset(&p.pull, 0, sizeof(p.pull));
   p.M = M;
@@ -895,13 +986,14 @@ int launch_conv(const drn_conv_desc& d, const void* x, const void* w, void* y, c
     return launch_variant<KC, BN, false, true>(epi, grid, kNumThreads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
   }
   if (p.pre_ss != nullptr) {
-    if constexpr (KC == 64 && (BN == 64 || BN == 128)) {
-      DRN_REQUIRE(d.R == 1 && d.S == 1 && d.pad_lo == 0 && d.pad_hi == 0 && view == nullptr,
-                  "conv_igemm: the BatchNorm prologue supports 1x1 convolutions only");
+    if constexpr ((KC == 64 && (BN == 64 || BN == 128)) || (KC == 32 && (BN == 32 || BN == 64)) ||
+                  (KC == 16 && (BN == 16 || BN == 32))) {
+      DRN_REQUIRE(view == nullptr, "conv_igemm: the BatchNorm prologue does not combine with an input view");
       return launch_variant<KC, BN, true, false>(epi, grid, kNumThreads + kPreThreads, smem_bytes, stream, tA,
                                                  tB, tC, tR, tR2, p);
     } else {
-      return fail("conv_igemm: the BatchNorm prologue needs C %% 64 == 0 and an N tile of 64 or 128 (got KC=%d BN=%d)", KC, BN);
+      return fail("conv_igemm: no BatchNorm-prologue variant for this tile (KC=%d BN=%d): C = 16 with N tiles 16/32, "
+                  "C = 32 with 32/64, C %% 64 == 0 with 64/128", KC, BN);
     }
   }
   return launch_variant<KC, BN, false, false>(epi, grid, kNumThreads, smem_bytes, stream, tA, tB, tC, tR, tR2, p);
@@ -950,11 +1042,17 @@ extern "C" int drn_conv_igemm(const drn_conv_desc* desc, const void* x, const vo
     // ordered pass (thread-local prologue / view / pull / two-side settings stay in force for the call).
     DRN_REQUIRE(y != nullptr && mode != DRN_EPI_BNBWD_APPLY,
                 "conv_igemm: statistics-only launches are not available in the deterministic mode");
+    const BnFin* fin = static_cast<const BnFin*>(current_bnfin());
+    current_bnfin() = nullptr;
     if (int rc = drn_conv_igemm(desc, x, w, y, side, nullptr, 0, bn_scale_shift, mode, force_bn, stream)) return rc;
     const long long M = 1LL * d.N * d.P * d.Q;
     if (mode == DRN_EPI_BNBWD || mode == DRN_EPI_BNBWD_ADD)   // (sum dm, sum dm * BatchNorm input)
       return drn_bn_pair_reduce(y, side, stats, stats_ld, M, d.K, stream);
-    return drn_bn_stats(y, stats, stats_ld, M, d.K, stream);
+    if (int rc = drn_bn_stats(y, stats, stats_ld, M, d.K, stream)) return rc;
+    if (fin != nullptr)   // the finalize the last CTA would have done
+      return drn_bn_finalize(stats, stats_ld, fin->count, fin->gamma, fin->beta, fin->run_mean, fin->run_var, fin->decay,
+                             fin->eps, fin->scale_shift, fin->mean_invstd, d.K, stream);
+    return 0;
   }
   int bn = force_bn;
   if (bn == 0) {
@@ -1148,6 +1246,44 @@ extern "C" int drn_conv_igemm_ex(const drn_conv_desc* desc, const drn_conv_view*
   current_pre() = nullptr;
   current_view() = nullptr;
   current_pull() = nullptr;
+  return rc;
+}
+
+// drn_conv_igemm_ex + "finalize the BatchNorm whose statistics this convolution accumulates": the last
+// CTA of the grid computes (scale, shift), (mean, 1/std) and the moving averages from the completed sums,
+// so a prologue-fused consumer can follow without a BatchNorm launch in between.
+extern "C" int drn_conv_igemm_fin(const drn_conv_desc* desc, const drn_conv_view* view,
+                                  const void* pre_scale_shift, const drn_pull_desc* pull, const drn_bn_fin* fin,
+                                  const void* x, const void* w, void* y, const void* side, float* stats,
+                                  int stats_ld, const void* bn_scale_shift, int mode, int force_bn, void* stream) {
+  using namespace drn;
+  BnFin f;
+  memset(&f, 0, sizeof(f));
+  if (fin != nullptr) {
+    DRN_REQUIRE(stats != nullptr && (mode == DRN_EPI_PLAIN || mode == DRN_EPI_RESADD),
+                "conv_igemm_fin: the finalize needs the forward statistics epilogue (PLAIN / RESADD with stats)");
+    DRN_REQUIRE(fin->counter != nullptr && fin->count > 0 && fin->gamma != nullptr && fin->beta != nullptr &&
+                    fin->scale_shift != nullptr && fin->mean_invstd != nullptr,
+                "conv_igemm_fin: counter, count, gamma, beta and both output tables are required");
+    DRN_REQUIRE((fin->run_mean == nullptr) == (fin->run_var == nullptr), "conv_igemm_fin: run_mean and run_var go together");
+    f.counter = fin->counter;
+    f.inv_count = (float)(1.0 / (double)fin->count);
+    f.unbias = fin->count > 1 ? (float)((double)fin->count / (double)(fin->count - 1)) : 1.f;
+    f.one_minus_decay = 1.f - fin->decay;
+    f.eps = fin->eps;
+    f.gamma = fin->gamma;
+    f.beta = fin->beta;
+    f.run_mean = fin->run_mean;
+    f.run_var = fin->run_var;
+    f.scale_shift = static_cast<float2*>(fin->scale_shift);
+    f.mean_invstd = static_cast<float2*>(fin->mean_invstd);
+    f.count = fin->count;
+    f.decay = fin->decay;
+    current_bnfin() = &f;
+  }
+  const int rc = drn_conv_igemm_ex(desc, view, pre_scale_shift, pull, x, w, y, side, stats, stats_ld, bn_scale_shift,
+                                   mode, force_bn, stream);
+  current_bnfin() = nullptr;
   return rc;
 }
 

@@ -41,6 +41,8 @@ struct WgradParams {
   float* dw;
   const float2* pre_ss;  // PRE: (scale, shift) per input channel, X is the RAW tensor
   unsigned int* det_sem; // deterministic mode: one semaphore per (Cout tile, column tile), else nullptr
+  int H_in, W_in;        // input plane (PRE: taps that fall into the zero padding stay zero)
+  int taps;              // PRE: 1 when a box can contain padding (filter larger than 1x1 or padded)
   int debug;             // DRN_WGRAD_DEBUG (timing experiments, wrong results): 1 = no red.global, 2 = no MMA
 };
 
@@ -226,40 +228,71 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
       // sits at physical chunk g ^ (r & 7)).  Out-of-range pixel rows need no masking here: their
       // dY rows are zero-filled by TMA, so whatever the transform makes of them is multiplied by 0.
       if constexpr (PRE) {
+        constexpr int kCPR = CWB / 8;                    // 16-byte chunks per row of a box
+        constexpr int kR = kPix * kCPR / kPreThreads;    // rows per thread and box (4 / 2 / 1)
+        constexpr int kRowStep = kPreThreads / kCPR;
+        constexpr int kSwzShift = CWB == 64 ? 0 : (CWB == 32 ? 1 : 2);
         const int tt = threadIdx.x - kThreads;
-        const int g = tt & 7;
-        const int r0 = tt >> 3;  // rows r0 + 16 * j
+        const int g = tt % kCPR;
+        const int r0 = tt / kCPR;  // rows r0 + kRowStep * j
+        uint32_t off[kR];
+#pragma unroll
+        for (int j = 0; j < kR; ++j) {
+          const int row = r0 + kRowStep * j;
+          off[j] = row * C_::kRBB + ((g ^ ((row >> kSwzShift) & (kCPR - 1))) << 4);
+        }
         int stage = 0;
         uint32_t phase = 0;
-        const int c_first = n0 % p.C;   // input channel of the first box (boxes wrap from tap to tap)
+        // first box of this CTA's column window: (tap row, tap column, channel); boxes wrap from tap to tap
+        const int tap_first = n0 / p.C, c_first = n0 - tap_first * p.C;
+        const int fr_first = tap_first / p.S, fs_first = tap_first - fr_first * p.S;
         for (int ch = 0; ch < n_chunks; ++ch) {
+          // (input row, input column) under tap (0,0) of my rows' output pixels: a tap that falls into
+          // the zero padding must stay zero after relu(0 * scale + shift).  (Rows beyond M need nothing:
+          // their dY rows are zero-filled by TMA, so whatever the transform makes of them is multiplied by 0.)
+          int ih0[kR], iw0[kR];
+          if (p.taps) {
+#pragma unroll
+            for (int j = 0; j < kR; ++j) {
+              const long long m = (long long)(chunk_begin + ch) * kPix + r0 + kRowStep * j;
+              const int rem = (int)(m % p.PQ);
+              const int op = rem / p.Q;
+              ih0[j] = op * p.stride - p.pad;
+              iw0[j] = (rem - op * p.Q) * p.stride - p.pad_w;
+            }
+          }
           mbar_wait(full_bar(stage), phase, 0x160 + stage);
           const uint32_t b_addr = sStages + stage * C_::kStageBytes + C_::kABytes;
-          int c0 = c_first;
-          for (int i = 0; i < nboxes; ++i, c0 = (c0 + CWB >= p.C) ? 0 : c0 + CWB) {
+          int c0 = c_first, fr = fr_first, fs = fs_first;
+          for (int i = 0; i < nboxes; ++i) {
             const float4* sp = reinterpret_cast<const float4*>(p.pre_ss + c0 + g * 8);
             float4 q[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) q[k] = __ldg(sp + k);
             const uint32_t box = b_addr + i * C_::kBBoxBytes;
-            uint4 v[kPix / 16];
+            uint4 v[kR];
 #pragma unroll
-            for (int j = 0; j < kPix / 16; ++j) {
-              const int row = r0 + 16 * j;
-              v[j] = ld_shared_v4(box + row * 128 + ((g ^ (row & 7)) << 4));
-            }
+            for (int j = 0; j < kR; ++j) v[j] = ld_shared_v4(box + off[j]);
 #pragma unroll
-            for (int j = 0; j < kPix / 16; ++j) {
+            for (int j = 0; j < kR; ++j) {
               uint32_t w[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
 #pragma unroll
               for (int k = 0; k < 4; ++k)
                 w[k] = pack_relu_bf16x2(fmaf(bf16lo(w[k]), q[k].x, q[k].y), fmaf(bf16hi(w[k]), q[k].z, q[k].w));
+              if (p.taps && (static_cast<unsigned>(ih0[j] + fr) >= static_cast<unsigned>(p.H_in) ||
+                             static_cast<unsigned>(iw0[j] + fs) >= static_cast<unsigned>(p.W_in)))
+                w[0] = w[1] = w[2] = w[3] = 0u;
               v[j] = make_uint4(w[0], w[1], w[2], w[3]);
             }
 #pragma unroll
-            for (int j = 0; j < kPix / 16; ++j) {
-              const int row = r0 + 16 * j;
-              st_shared_v4(box + row * 128 + ((g ^ (row & 7)) << 4), v[j].x, v[j].y, v[j].z, v[j].w);
+            for (int j = 0; j < kR; ++j) st_shared_v4(box + off[j], v[j].x, v[j].y, v[j].z, v[j].w);
+            c0 += CWB;
+            if (c0 >= p.C) {
+              c0 = 0;
+              if (++fs == p.S) {
+                fs = 0;
+                ++fr;
+              }
             }
           }
           fence_proxy_async_smem();
@@ -379,6 +412,9 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
   p.C = d.C;
   p.dw = dw;
   p.pre_ss = reinterpret_cast<const float2*>(current_pre());
+  p.H_in = d.H;
+  p.W_in = d.W;
+  p.taps = (d.R * d.S > 1 || d.pad_lo != 0 || d.pad_hi != 0) ? 1 : 0;
 
   CUtensorMap tDY, tX;
   if (int e = tmap_tiled_2d(&tDY, dy, 2, (uint64_t)M, d.K, d.K, kPix, CWA, C_::kRBA)) return e;
@@ -395,19 +431,16 @@ int launch_wgrad(const drn_conv_desc& d, const void* x, const void* dy, float* d
   }
   const int grid = units * splits;
   if (p.pre_ss != nullptr) {
-    if constexpr (CWB == 64) {
-      static PerDeviceOnce attr_set_pre;
-      if (attr_set_pre.need()) {
-        DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<CWA, CWB, true>,
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, C_::kSmemBytes));
-        attr_set_pre.mark();
-      }
-      DRN_CHECK_CUDA(launch_pdl_conv(conv_wgrad_kernel<CWA, CWB, true>, dim3(grid), dim3(kThreads + kPreThreads),
-                                     C_::kSmemBytes, stream, tDY, tX, p));
-      return 0;
-    } else {
-      return fail("conv_wgrad: the BatchNorm prologue needs C %% 64 == 0");
+    DRN_REQUIRE(view == nullptr, "conv_wgrad: the BatchNorm prologue does not combine with an input view");
+    static PerDeviceOnce attr_set_pre;
+    if (attr_set_pre.need()) {
+      DRN_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<CWA, CWB, true>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, C_::kSmemBytes));
+      attr_set_pre.mark();
     }
+    DRN_CHECK_CUDA(launch_pdl_conv(conv_wgrad_kernel<CWA, CWB, true>, dim3(grid), dim3(kThreads + kPreThreads),
+                                   C_::kSmemBytes, stream, tDY, tX, p));
+    return 0;
   }
   DRN_CHECK_CUDA(launch_pdl_conv(conv_wgrad_kernel<CWA, CWB>, dim3(grid), dim3(kThreads), C_::kSmemBytes, stream,
                             tDY, tX, p));
@@ -450,7 +483,7 @@ extern "C" int drn_conv_wgrad_view(const drn_conv_desc* desc, const drn_conv_vie
 
 // dw += dY (x) relu(x * scale + shift): filter gradient of a convolution whose input is the
 // BatchNorm+ReLU of the RAW tensor x - the activation is rebuilt in shared memory (see
-// drn_conv_igemm_pre), so the forward pass never has to store it.  C % 64 == 0.
+// drn_conv_igemm_pre), so the forward pass never has to store it.  Any filter size / stride.
 extern "C" int drn_conv_wgrad_pre(const drn_conv_desc* desc, const void* x, const void* pre_scale_shift,
                                   const void* dy, float* dw, int split_k, void* stream) {
   if (pre_scale_shift == nullptr || (reinterpret_cast<uintptr_t>(pre_scale_shift) & 15) != 0)

@@ -31,6 +31,14 @@ class PullDesc(ctypes.Structure):
                 ("bucket", ctypes.c_int), ("off", ctypes.c_longlong), ("count", ctypes.c_longlong)]
 
 
+class BnFin(ctypes.Structure):
+    """drn_bn_fin (include/drn_b200.h): BatchNorm finalize done by the last CTA of the producing convolution."""
+    _fields_ = [("counter", ctypes.c_void_p), ("count", ctypes.c_longlong), ("gamma", ctypes.c_void_p),
+                ("beta", ctypes.c_void_p), ("run_mean", ctypes.c_void_p), ("run_var", ctypes.c_void_p),
+                ("decay", ctypes.c_float), ("eps", ctypes.c_float), ("scale_shift", ctypes.c_void_p),
+                ("mean_invstd", ctypes.c_void_p)]
+
+
 class ConvView(ctypes.Structure):
     _fields_ = [("stride_w", ctypes.c_longlong), ("stride_h", ctypes.c_longlong),
                 ("stride_n", ctypes.c_longlong), ("pad_w_lo", ctypes.c_int), ("pad_w_hi", ctypes.c_int)]
@@ -57,6 +65,7 @@ _SIGNATURES = {
     "drn_conv_igemm": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_wgrad": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _i, _vp]),
     "drn_conv_igemm_ex": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, ctypes.POINTER(PullDesc), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
+    "drn_conv_igemm_fin": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, ctypes.POINTER(PullDesc), ctypes.POINTER(BnFin), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_conv_igemm_epi2": (_i, [ctypes.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp]),
     "drn_conv_igemm_view": (_i, [ctypes.POINTER(ConvDesc), ctypes.POINTER(ConvView), _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
     "drn_resize_crop_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp]),

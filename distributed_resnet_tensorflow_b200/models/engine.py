@@ -46,25 +46,65 @@ DGRAD_S2_PHASES = os.environ.get("DRN_DGRAD_S2", "1") != "0"
 _DEBUG_SKIP = frozenset(filter(None, os.environ.get("DRN_DEBUG_SKIP", "").split(",")))
 
 
-def _fuse_bn0(blk: BlockSpec) -> bool:
+# BatchNorm+ReLU as a prologue of the consuming convolution (and of its filter gradient):
+#   DRN_FUSE_PRE=default  the measured policy below (first 1x1 convolution of the 256/512-channel bottlenecks)
+#   DRN_FUSE_PRE=all      every convolution for which a prologue variant exists (any filter size, 16/32/64k
+#                         channels): no standalone BatchNorm pass is left in the forward pass
+#   DRN_FUSE_PRE=none     never (same as DRN_FUSE_BN0=0)
+# Measured on one B200 (bench/run_r2_pre.sh, profiles/fuse_pre_all_r2.txt): "all" is correct (oracle tests
+# pass with it) and SLOWER everywhere - CIFAR-50 966 -> 710-726 steps/s at 16 images, 534 -> 396 at 128,
+# ImageNet-50 14 539 -> 10 660 img/s: a 3x3 layer re-activates its tile once per filter tap, and the
+# transform hop (TMA -> four warps -> MMA) adds latency to every k-step of the short 16/32-channel reductions,
+# which costs more than the BatchNorm launches it removes.
+FUSE_PRE = os.environ.get("DRN_FUSE_PRE", "default")
+# the BatchNorm finalize (sums -> scale/shift, moving averages) done by the last CTA of the convolution that
+# accumulates the sums, when the consumer of that BatchNorm is prologue-fused (no launch in between).
+# Measured: 726 -> 710 steps/s (CIFAR, all fused), noise on ImageNet - the serial tail of the last CTA costs
+# what the tiny launch did.  Off by default.
+FIN_IN_CONV = os.environ.get("DRN_FIN_IN_CONV", "0") != "0"
+
+
+def _pre_supported(cin: int, cout: int) -> bool:
+    """A prologue variant of the implicit-GEMM kernel exists (csrc/conv_igemm.cu: launch_conv)."""
+    if cin == 16:
+        return cout in (16, 32)
+    if cin == 32:
+        return cout in (32, 64)
+    return cin % 64 == 0 and cout % 64 == 0
+
+
+def _fuse_all(blk: BlockSpec, small_images: bool) -> bool:
+    return FUSE_PRE == "all"
+
+
+def _fuse_bn0(blk: BlockSpec, small_images: bool = False) -> bool:
     """Where the prologue variant is a measured win (bench/prof_pre.py and bench.py A/B on one B200):
     1x1 first convolution over 256 or 512 input channels (at 1024 the A tile is re-transformed once
     per 128-column N tile and the gain vanishes); with a projection shortcut only at 256 channels."""
     c0 = blk.convs[0]
-    if not FUSE_BN0 or c0.ksize != 1 or c0.stride != 1 or len(blk.convs) != 3:
+    if not FUSE_BN0 or FUSE_PRE == "none":
+        return False
+    if _fuse_all(blk, small_images):
+        return _pre_supported(c0.cin, c0.cout) and (blk.proj is None or _pre_supported(blk.proj.cin, blk.proj.cout))
+    if c0.ksize != 1 or c0.stride != 1 or len(blk.convs) != 3:
         return False
     if blk.cin not in (256, 512, 1024) or blk.cin > int(os.environ.get("DRN_FUSE_BN0_MAXC", "512")):
         return False
     return blk.proj is None or blk.cin == 256
 
 
-def _fuse_bn_last(blk: BlockSpec) -> bool:
-    """The BatchNorm+ReLU in front of a bottleneck block's LAST (1x1) convolution applied by that
-    convolution's prologue (and by its filter gradient's) to the raw output of the 3x3 convolution,
-    so that activation is never stored.  DRN_FUSE_BN2 = largest channel count to fuse (0 = off)."""
-    c = blk.convs[-1]
+def _fuse_inner(blk: BlockSpec, i: int, small_images: bool = False) -> bool:
+    """The BatchNorm+ReLU in front of convolution i >= 1 of the block applied by that convolution's
+    prologue (and by its filter gradient's) to the raw output of convolution i-1, so the activation is
+    never stored.  ImageNet: off (DRN_FUSE_BN2 = largest channel count to fuse in front of a bottleneck's
+    last 1x1 convolution; measured no gain, profiles/ceilings_and_fuse_bn2_r2.txt)."""
+    c = blk.convs[i]
+    if FUSE_PRE == "none":
+        return False
+    if _fuse_all(blk, small_images):
+        return _pre_supported(c.cin, c.cout)
     maxc = int(os.environ.get("DRN_FUSE_BN2", "0"))
-    return len(blk.convs) == 3 and c.ksize == 1 and c.stride == 1 and c.cin % 64 == 0 and c.cin <= maxc
+    return (len(blk.convs) == 3 and i == 2 and c.ksize == 1 and c.stride == 1 and c.cin % 64 == 0 and c.cin <= maxc)
 
 
 def _fuse_bnbwd(blk: BlockSpec) -> bool:
@@ -232,6 +272,16 @@ class _BN:
         self.ss = torch.zeros((C, 2), device=eng.device)
         self.mi = torch.zeros((C, 2), device=eng.device)
         self.coef = torch.zeros((C, 4), device=eng.device)
+        self.fin_counter = eng.alloc_fin_counter()
+        self._fin = None
+
+    def fin(self, count: int):
+        """drn_bn_fin for a convolution that accumulates this BatchNorm's forward sums over ``count``
+        elements per channel (training mode: moving averages are updated)."""
+        if self._fin is None or self._fin.count != count:
+            self._fin = _nl.BnFin(_p(self.fin_counter), count, _p(self.gamma), _p(self.beta), _p(self.run_mean),
+                                  _p(self.run_var), BN_DECAY, BN_EPS, _p(self.ss), _p(self.mi))
+        return self._fin
 
 
 class _Conv:
@@ -296,6 +346,10 @@ class NativeResNet:
         self._stats_chunks: List[torch.Tensor] = []
         self._stats_arena = torch.zeros(2 * 2 * sum(b.channels for b in spec.bns()) * 2 + 4096, device=dev)
         self._stats_off = 0
+        self._fin_counters = torch.zeros(len(list(spec.bns())) + 8, dtype=torch.int32, device=dev)
+        self._fin_next = 0
+        self._prefinalized = set()      # BatchNorms whose finalize ran inside the producing convolution (this forward)
+        self.small_images = spec.dataset != "imagenet"
         self._wd_arena = torch.zeros(self.layout.total + 64 * len(self.layout.order), dtype=torch.bfloat16, device=dev)
         self._wd_off = 0
         self._wd_entries: List[Tuple[str, int]] = []
@@ -332,6 +386,12 @@ class NativeResNet:
         self._stats_off += 2 * C
         assert self._stats_off <= self._stats_arena.numel()
         return self._stats_arena[off:off + 2 * C].view(2, C)
+
+    def alloc_fin_counter(self) -> torch.Tensor:
+        i = self._fin_next
+        self._fin_next += 1
+        assert self._fin_next <= self._fin_counters.numel()
+        return self._fin_counters[i:i + 1]
 
     def _act(self, n, h, w, c, dtype=torch.bfloat16):
         return torch.empty((n, h, w, c), dtype=dtype, device=self.device)
@@ -406,9 +466,9 @@ class NativeResNet:
         B = self.B
         d = {"spec": blk}
         d["bn0"] = _BN(blk.bns[0], self)
-        d["fuse"] = _fuse_bn0(blk)
+        d["fuse"] = _fuse_bn0(blk, self.small_images)
         d["fuse_bwd"] = _fuse_bnbwd(blk)
-        d["fuse_last"] = _fuse_bn_last(blk)
+        d["fuse_in"] = [d["fuse"]] + [_fuse_inner(blk, i, self.small_images) for i in range(1, len(blk.convs))]
         d["a0"] = None if d["fuse"] else self._act(B, blk.hin, blk.hin, blk.cin)
         sizes = [B * blk.hin * blk.hin * blk.cin]
         if blk.proj is not None:
@@ -426,7 +486,7 @@ class NativeResNet:
             sizes.append(y.numel())
             if not last:
                 bns.append(_BN(blk.bns[i + 1], self))
-                fused = d["fuse_last"] and i + 2 == len(blk.convs)    # consumed raw by the last convolution
+                fused = d["fuse_in"][i + 1]    # consumed raw by the next convolution's prologue
                 acts.append(None if fused else self._act(B, c.hout, c.hout, c.cout))
         d.update(convs=convs, bns=bns, ys=ys, acts=acts, max_elems=max(sizes))
         return d
@@ -526,9 +586,17 @@ class NativeResNet:
         return self.pull_plan.get(f"{conv_name}/kernel") if (self.pull_plan is not None and conv_name) else None
 
     def _conv(self, desc, x, w, y, side=None, stats=None, ss=None, mode=EPI_PLAIN, pre=None, pull=None,
-              view=None):
+              view=None, fin=None):
         """``pre``: (scale, shift) table of a BatchNorm+ReLU to apply to ``x`` on the fly; ``pull``:
-        drn_pull_desc of the layer when its weights are still on the parameter-server shards."""
+        drn_pull_desc of the layer when its weights are still on the parameter-server shards; ``fin``:
+        the _BN whose sums go to ``stats`` and whose finalize the kernel's last CTA should do."""
+        if fin is not None and stats is not None:
+            count = y.numel() // fin.C
+            _nl.call("drn_conv_igemm_fin", ctypes.byref(desc), ctypes.byref(view) if view is not None else None,
+                     _p(pre), ctypes.byref(pull) if pull is not None else None, ctypes.byref(fin.fin(count)),
+                     _p(x), _p(w), _p(y), _p(side), _p(stats), stats.stride(0), _p(ss), mode, 0, self._st())
+            self._prefinalized.add(id(fin))
+            return
         if pull is not None or view is not None:
             _nl.call("drn_conv_igemm_ex", ctypes.byref(desc), ctypes.byref(view) if view is not None else None,
                      _p(pre), ctypes.byref(pull) if pull is not None else None, _p(x), _p(w), _p(y), _p(side),
@@ -541,9 +609,19 @@ class NativeResNet:
         _nl.call("drn_conv_igemm", ctypes.byref(desc), _p(x), _p(w), _p(y), _p(side), _p(stats),
                  stats.stride(0) if stats is not None else 0, _p(ss), mode, 0, self._st())
 
-    def _stem_conv(self, stats) -> None:
+    def _stem_conv(self, stats, fin=None) -> None:
         self._conv(self.stem.desc, self.x0, self.stem.w, self.y_stem, stats=stats,
-                   pull=self._pull(self.spec.stem.name), view=self.stem_view)
+                   pull=self._pull(self.spec.stem.name), view=self.stem_view, fin=fin)
+
+    def _fin_for(self, bn: _BN, consumer_fused: bool, training: bool):
+        """The BatchNorm to finalize inside the convolution that produces its sums: only when nothing but
+        prologue-fused consumers read its tables next (a standalone bn_finalize_apply finalizes itself)."""
+        return bn if (FIN_IN_CONV and training and consumer_fused) else None
+
+    def _finalize_once(self, bn: _BN, count: int, training: bool) -> None:
+        if id(bn) in self._prefinalized:
+            return
+        self._bn_finalize(bn, count, training)
 
     def _event(self):
         if self._ev_next == len(self._ev_pool):
@@ -633,6 +711,7 @@ class NativeResNet:
         st = self._st()
         if self.pre_forward is not None:
             self.pre_forward(self)
+        self._prefinalized.clear()
         if training:
             self._stats_arena.zero_()
             self._ev_next = 0
@@ -650,15 +729,19 @@ class NativeResNet:
                          self.pool_out.numel() // g.K, g.K, st)
             x = self.pool_out
         else:
-            self._stem_conv(first_bn.fstats if training else None)
+            self._stem_conv(first_bn.fstats if training else None,
+                            fin=self._fin_for(first_bn, self.blocks[0]["fuse"], training))
             x = self.y_stem
         for i, b in enumerate(self.blocks):
-            nxt = self.blocks[i + 1]["bn0"] if i + 1 < len(self.blocks) else self.final_bn
-            x = self._block_fwd(b, x, nxt, training)
+            last_block = i + 1 == len(self.blocks)
+            nxt = self.final_bn if last_block else self.blocks[i + 1]["bn0"]
+            # (the final BatchNorm is applied inside the pooling kernel: only its tables are needed)
+            nxt_fused = True if last_block else self.blocks[i + 1]["fuse"]
+            x = self._block_fwd(b, x, nxt, training, nxt_fused)
         self.x_final = x
         fb = self.final_bn
         hw = x.shape[1] * x.shape[2]
-        self._bn_finalize(fb, x.numel() // fb.C, training)
+        self._finalize_once(fb, x.numel() // fb.C, training)
         _nl.call("drn_bnrelu_avgpool", _p(x), _p(fb.ss), _p(self.pooled), self.B, hw, fb.C, st)
         self._conv(self.dense_desc, self.pooled, self.dense_w, self.logits, pull=self._pull("dense"))
         if training and self.pull_plan is not None:
@@ -666,13 +749,15 @@ class NativeResNet:
             # has fetched its weights, i.e. after the forward pass
             self._on_wgrad_stream(self.prep_dgrad_weights, None)
 
-    def _block_fwd(self, b: dict, x, next_bn: _BN, training: bool):
+    def _block_fwd(self, b: dict, x, next_bn: _BN, training: bool, next_fused: bool = False):
         bn0 = b["bn0"]
         b["x"] = x
+        fuse_in = b["fuse_in"]
         if b["fuse"]:
-            # only the per-channel scale/shift (and the moving averages) are computed here; the
-            # consumers of relu(bn0(x)) apply it to their tiles of the raw x in shared memory
-            self._bn_finalize(bn0, x.numel() // bn0.C, training)
+            # only the per-channel scale/shift (and the moving averages) are computed - by the convolution
+            # that produced x or here; the consumers of relu(bn0(x)) apply it to their tiles of the raw x
+            # in shared memory
+            self._finalize_once(bn0, x.numel() // bn0.C, training)
             h, pre = x, bn0.ss
         else:
             self._bn_fwd(bn0, x, b["a0"], training)
@@ -683,23 +768,24 @@ class NativeResNet:
             self._conv(pj.desc, h, pj.w, b["shortcut"], pre=pre, pull=self._pull(pj.spec.name))
             shortcut = b["shortcut"]
         convs = b["convs"]
-        pre_last = None
         for i, c in enumerate(convs):
             last = i + 1 == len(convs)
             y = b["ys"][i]
             if last:
-                self._conv(c.desc, h, c.w, y, side=shortcut, mode=EPI_RESADD, pre=pre_last,
-                           stats=next_bn.fstats if training else None, pull=self._pull(c.spec.name))
+                self._conv(c.desc, h, c.w, y, side=shortcut, mode=EPI_RESADD, pre=pre,
+                           stats=next_bn.fstats if training else None, pull=self._pull(c.spec.name),
+                           fin=self._fin_for(next_bn, next_fused, training))
             else:
                 bn = b["bns"][i]
-                self._conv(c.desc, h, c.w, y, stats=bn.fstats if training else None, pre=pre if i == 0 else None,
-                           pull=self._pull(c.spec.name))
-                if b.get("fuse_last") and i + 2 == len(convs):
-                    self._bn_finalize(bn, y.numel() // bn.C, training)
-                    h, pre_last = y, bn.ss
+                fused = fuse_in[i + 1]
+                self._conv(c.desc, h, c.w, y, stats=bn.fstats if training else None, pre=pre,
+                           pull=self._pull(c.spec.name), fin=self._fin_for(bn, fused, training))
+                if fused:
+                    self._finalize_once(bn, y.numel() // bn.C, training)
+                    h, pre = y, bn.ss
                 else:
                     self._bn_fwd(bn, y, b["acts"][i], training)
-                    h = b["acts"][i]
+                    h, pre = b["acts"][i], None
         return b["ys"][-1]
 
     # ---- loss ---------------------------------------------------------------------------------

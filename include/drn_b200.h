@@ -103,8 +103,9 @@ int drn_conv_igemm_view(const drn_conv_desc* desc, const drn_conv_view* view, co
 
 /* y = conv(relu(x * scale + shift), w): BatchNorm + ReLU of the consuming layer applied to the A tile
  * in shared memory (four extra warps between the TMA load and the MMA), so the activated tensor is
- * never materialised.  pre_scale_shift = float2[C], 16-byte aligned.  1x1 convolutions, C % 64 == 0,
- * N tile 64 or 128. */
+ * never materialised.  pre_scale_shift = float2[C], 16-byte aligned.  Any filter size / stride (taps
+ * that fall into the zero padding stay zero); C = 16 (N tiles 16/32), 32 (32/64) or a multiple of 64
+ * (64/128). */
 int drn_conv_igemm_pre(const drn_conv_desc* desc, const void* x, const void* pre_scale_shift,
                        const void* w, void* y, const void* side, float* stats, int stats_ld,
                        const void* bn_scale_shift, int mode, int force_bn, void* stream);
@@ -131,6 +132,28 @@ int drn_conv_igemm_ex(const drn_conv_desc* desc, const drn_conv_view* view, cons
                       const drn_pull_desc* pull, const void* x, const void* w, void* y, const void* side,
                       float* stats, int stats_ld, const void* bn_scale_shift, int mode, int force_bn,
                       void* stream);
+
+/* BatchNorm finalize folded into the convolution that produces the statistics: the last CTA of the
+ * grid to finish turns the completed sums into (scale, shift), (mean, 1/std) and the moving averages
+ * (the arithmetic of drn_bn_finalize), so a prologue-fused consumer needs no BatchNorm launch in
+ * between.  counter: one zero-initialised device word per BatchNorm (the kernel resets it).
+ * (Reference: tf.layers.batch_normalization, resnet_model_official.py:41-50.) */
+typedef struct {
+  unsigned int* counter;
+  long long count;           /* elements per channel (N*P*Q) */
+  const float* gamma;
+  const float* beta;
+  float* run_mean;           /* NULL: no moving-average update */
+  float* run_var;
+  float decay, eps;
+  void* scale_shift;         /* out float2[K] */
+  void* mean_invstd;         /* out float2[K] */
+} drn_bn_fin;
+/* drn_conv_igemm_ex + finalize (fin may be NULL); PLAIN / RESADD epilogues with stats != NULL. */
+int drn_conv_igemm_fin(const drn_conv_desc* desc, const drn_conv_view* view, const void* pre_scale_shift,
+                       const drn_pull_desc* pull, const drn_bn_fin* fin, const void* x, const void* w, void* y,
+                       const void* side, float* stats, int stats_ld, const void* bn_scale_shift, int mode,
+                       int force_bn, void* stream);
 
 /* Data gradient (K2) of the convolution described by `desc` (FORWARD geometry):
  *   dx[N,H,W,C] = sum_{k,r,s} dy[N,P,Q,K] (x) w,  given w_dgrad = drn_weight_prep_dgrad(w).

@@ -234,18 +234,24 @@ def test_view_entry_points_equal_the_dense_4x4_convolution():
     assert (dw.t - refw).abs().max() <= 2e-3 * refw.abs().max() + 1e-3
 
 
-@pytest.mark.parametrize("N,H,C,K,st", [(8, 14, 256, 128, 1), (5, 7, 512, 64, 1), (4, 28, 256, 512, 2),
-                                        (3, 56, 64, 256, 1)])
-def test_conv_with_batchnorm_prologue_equals_apply_then_conv(N, H, C, K, st):
+PRE_CASES = [(8, 14, 256, 128, 1, 1), (5, 7, 512, 64, 1, 1), (4, 28, 256, 512, 1, 2), (3, 56, 64, 256, 1, 1),
+         # filters larger than 1x1 (taps in the zero padding must stay zero) and the 16 / 32-channel tiles
+         (4, 32, 16, 16, 3, 1), (4, 32, 16, 32, 3, 2), (4, 32, 16, 32, 1, 2), (4, 16, 32, 32, 3, 1),
+         (4, 16, 32, 64, 3, 2), (5, 8, 64, 64, 3, 1), (3, 14, 256, 256, 3, 1), (3, 28, 128, 128, 3, 2),
+         (2, 7, 512, 512, 3, 1)]
+
+
+@pytest.mark.parametrize("N,H,C,K,ks,st", PRE_CASES)
+def test_conv_with_batchnorm_prologue_equals_apply_then_conv(N, H, C, K, ks, st):
     """drn_conv_igemm_pre (BN+ReLU applied to the A tile in shared memory) against drn_bn_apply
     followed by the plain convolution: identical bf16 inputs to the tensor core, so the outputs and
     the fused statistics must agree to rounding of the accumulation order."""
     from distributed_resnet_tensorflow_b200.ops.conv import ConvGeom
     nl = _nl()
-    g = ConvGeom.tf_fixed_padding(N, H, H, C, K, 1, st)
+    g = ConvGeom.tf_fixed_padding(N, H, H, C, K, ks, st)
     gen = torch.Generator(device="cuda").manual_seed(6)
     x = (torch.randn((N, H, H, C), device="cuda", generator=gen) * 1.5).bfloat16()
-    w = (torch.randn((K, 1, 1, C), device="cuda", generator=gen) / C ** 0.5).bfloat16()
+    w = (torch.randn((K, ks, ks, C), device="cuda", generator=gen) / (ks * ks * C) ** 0.5).bfloat16()
     ss = torch.stack([torch.rand(C, device="cuda", generator=gen) + 0.5,
                       torch.randn(C, device="cuda", generator=gen) * 0.3], 1).contiguous()
     a = torch.empty_like(x)
@@ -262,17 +268,17 @@ def test_conv_with_batchnorm_prologue_equals_apply_then_conv(N, H, C, K, st):
     assert (got.t.float() - want.float()).abs().max() <= 0.01 * want.float().abs().max() + 1e-3
     assert torch.allclose(st_got, st_want, rtol=2e-3, atol=0.5)
     # first principles
-    ref = F.conv2d(torch.relu(x.float() * ss[:, 0] + ss[:, 1]).permute(0, 3, 1, 2),
-                   w.float().permute(0, 3, 1, 2), stride=st).permute(0, 2, 3, 1)
+    act = torch.relu(x.float() * ss[:, 0] + ss[:, 1]).permute(0, 3, 1, 2)
+    act = F.pad(act, (g.pad_lo, g.pad_hi, g.pad_lo, g.pad_hi))     # zero padding AFTER the activation
+    ref = F.conv2d(act, w.float().permute(0, 3, 1, 2), stride=st).permute(0, 2, 3, 1)
     assert (got.t.float() - ref).abs().max() <= 0.03 * ref.abs().max() + 1e-3
 
 
-@pytest.mark.parametrize("N,H,C,K,st", [(8, 14, 256, 128, 1), (5, 7, 512, 64, 1), (4, 28, 256, 512, 2),
-                                        (3, 56, 64, 256, 1)])
-def test_wgrad_with_batchnorm_prologue_equals_apply_then_wgrad(N, H, C, K, st):
+@pytest.mark.parametrize("N,H,C,K,ks,st", PRE_CASES)
+def test_wgrad_with_batchnorm_prologue_equals_apply_then_wgrad(N, H, C, K, ks, st):
     from distributed_resnet_tensorflow_b200.ops.conv import ConvGeom
     nl = _nl()
-    g = ConvGeom.tf_fixed_padding(N, H, H, C, K, 1, st)
+    g = ConvGeom.tf_fixed_padding(N, H, H, C, K, ks, st)
     gen = torch.Generator(device="cuda").manual_seed(7)
     x = (torch.randn((N, H, H, C), device="cuda", generator=gen) * 1.5).bfloat16()
     dy = torch.randn((N, g.P, g.Q, K), device="cuda", generator=gen).bfloat16()
@@ -281,9 +287,9 @@ def test_wgrad_with_batchnorm_prologue_equals_apply_then_wgrad(N, H, C, K, st):
     a = torch.empty_like(x)
     nl.call("drn_bn_apply", _p(x), _p(ss), 0, _p(a), N * H * H, C, 1, _st())
     d = g.desc()
-    want = torch.zeros((K, 1, 1, C), device="cuda")
+    want = torch.zeros((K, ks, ks, C), device="cuda")
     nl.call("drn_conv_wgrad", ctypes.byref(d), _p(a), _p(dy), _p(want), 0, _st())
-    got = Guarded((K, 1, 1, C), torch.float32)
+    got = Guarded((K, ks, ks, C), torch.float32)
     got.t.zero_()
     nl.call("drn_conv_wgrad_pre", ctypes.byref(d), _p(x), _p(ss), _p(dy), _p(got.t), 0, _st())
     torch.cuda.synchronize()
@@ -364,3 +370,41 @@ def test_cta_pair_kernel_equals_single_cta_kernel(N, H, C, K, ks, mode, bn, monk
     elif mode == 2:
         ref = ref * ((side.float() * ss[:, 0] + ss[:, 1]) > 0)
     assert (outs[1][0].float() - ref).abs().max() <= 0.02 * ref.abs().max() + 1e-3
+
+
+@pytest.mark.parametrize("N,H,C,K,ks,mode", [(16, 32, 16, 16, 3, 0), (8, 16, 32, 64, 3, 1), (6, 14, 256, 1024, 1, 1),
+                                             (128, 8, 64, 64, 3, 0), (2, 56, 64, 256, 1, 1)])
+def test_finalize_by_the_last_cta_equals_bn_finalize(N, H, C, K, ks, mode):
+    """drn_conv_igemm_fin: the last CTA of the statistics-producing convolution computes (scale, shift),
+    (mean, 1/std) and the moving averages; against drn_bn_finalize on the same sums.  Twice in a row:
+    the counter must come back to zero."""
+    from distributed_resnet_tensorflow_b200._native.lib import BnFin
+    from distributed_resnet_tensorflow_b200.ops.conv import ConvGeom
+    nl = _nl()
+    g = ConvGeom.tf_fixed_padding(N, H, H, C, K, ks, 1)
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn((N, H, H, C), device="cuda", generator=gen).bfloat16()
+    w = (torch.randn((K, ks, ks, C), device="cuda", generator=gen) / (ks * ks * C) ** 0.5).bfloat16()
+    side = torch.randn((N, g.P, g.Q, K), device="cuda", generator=gen).bfloat16() if mode else None
+    gamma = torch.rand(K, device="cuda", generator=gen) + 0.5
+    beta = torch.randn(K, device="cuda", generator=gen)
+    d = g.desc()
+    count = N * g.P * g.Q
+    y = torch.empty((N, g.P, g.Q, K), dtype=torch.bfloat16, device="cuda")
+    counter = torch.zeros(1, dtype=torch.int32, device="cuda")
+    rm, rv = torch.zeros(K, device="cuda"), torch.ones(K, device="cuda")
+    rm2, rv2 = rm.clone(), rv.clone()
+    for _ in range(2):
+        stats = torch.zeros((2, K), device="cuda")
+        ss, mi = torch.zeros((K, 2), device="cuda"), torch.zeros((K, 2), device="cuda")
+        fin = BnFin(_p(counter), count, _p(gamma), _p(beta), _p(rm), _p(rv), 0.9, 1e-5, _p(ss), _p(mi))
+        nl.call("drn_conv_igemm_fin", ctypes.byref(d), None, 0, None, ctypes.byref(fin), _p(x), _p(w), _p(y),
+                _p(side) if side is not None else 0, _p(stats), K, 0, mode, 0, _st())
+        ss2, mi2 = torch.zeros_like(ss), torch.zeros_like(mi)
+        nl.call("drn_bn_finalize", _p(stats), K, count, _p(gamma), _p(beta), _p(rm2), _p(rv2), 0.9, 1e-5, _p(ss2),
+                _p(mi2), K, _st())
+        torch.cuda.synchronize()
+        assert int(counter) == 0
+        assert torch.equal(ss, ss2) and torch.equal(mi, mi2)
+        assert torch.equal(rm, rm2) and torch.equal(rv, rv2)
+        assert float(ss.abs().sum()) > 0
