@@ -26,3 +26,7 @@ for H, C, K, s in ((56, 256, 64, 1), (28, 512, 128, 1), (14, 1024, 256, 1), (7, 
     tc = t(lambda: nl.call("drn_conv_igemm", ctypes.byref(d), p(a), p(w), p(y), 0, p(sb), K, 0, 0, 0, st()))
     tp = t(lambda: nl.call("drn_conv_igemm_pre", ctypes.byref(d), p(x), p(ss), p(w), p(y), 0, p(sb), K, 0, 0, 0, st()))
     print(f"H={H:2d} C={C:4d} K={K:4d} s{s}: bn_apply {ta:6.1f} us + conv {tc:6.1f} us = {ta+tc:6.1f} | conv_pre {tp:6.1f} us", flush=True)
+    dy = torch.randn((N, g.P, g.Q, K), device="cuda").bfloat16(); dw = torch.zeros((K, 1, 1, C), device="cuda")
+    tw = t(lambda: nl.call("drn_conv_wgrad", ctypes.byref(d), p(a), p(dy), p(dw), 0, st()))
+    twp = t(lambda: nl.call("drn_conv_wgrad_pre", ctypes.byref(d), p(x), p(ss), p(dy), p(dw), 0, st()))
+    print(f"                          wgrad {tw:6.1f} us | wgrad_pre {twp:6.1f} us", flush=True)
