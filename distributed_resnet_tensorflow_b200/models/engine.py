@@ -19,7 +19,6 @@ Gradient averaging across replicas, the optimizer step and the PS-style sharded 
 from __future__ import annotations
 
 import ctypes
-import math
 import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
@@ -28,8 +27,7 @@ import numpy as np
 import torch
 
 from .._native import lib as _nl
-from .._native.lib import (ConvDesc, ConvView, EPI_BNBWD, EPI_BNBWD_ADD, EPI_BNBWD_APPLY, EPI_PLAIN, EPI_RESADD,
-                           PullDesc)
+from .._native.lib import EPI_BNBWD, EPI_BNBWD_ADD, EPI_BNBWD_APPLY, EPI_PLAIN, EPI_RESADD
 from ..ops.conv import ConvGeom
 from .spec import BlockSpec, BNSpec, ConvSpec, NetSpec
 

@@ -17,12 +17,12 @@ projection conv, projection bn), see models/spec.py.
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional
+from typing import List
 
 import torch
 
 from .._native import lib as _nl
-from .._native.lib import EPI_BNBWD, EPI_PLAIN, EPI_RESADD
+from .._native.lib import EPI_BNBWD, EPI_RESADD
 from ..ops.conv import ConvGeom
 from .engine import (NativeResNet, WGRAD_SIDE_STREAM, _BN, _Conv, _p, padded_classes)
 from .spec import BlockSpec

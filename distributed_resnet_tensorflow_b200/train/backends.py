@@ -12,7 +12,7 @@ Both expose ``train_step(batch, lr) -> metrics``, ``eval_batch``, ``export_varia
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional, Tuple
+from typing import Dict, Optional, Tuple
 
 import numpy as np
 import torch
