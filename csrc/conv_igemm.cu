@@ -482,7 +482,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     const uint32_t n_res = p.n_res;
     float2* my_ss = sScaleShift + grp * 256;
     float4* my_coef = sCoef + grp * 256;
-    float* my_red = reinterpret_cast<float*>(sScaleShift + 512) + grp * 256;  // [2][kHalf*kCW]
     constexpr int kHalf = C_::kChunks >= 2 ? C_::kChunks / 2 : 1;  // chunks per tile per group
     // swizzled byte offsets of my row's 16-byte pieces inside a staging buffer (chunk independent)
     uint32_t row_off[kRowBytes / 16];
@@ -507,12 +506,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
 
     // Reduce the per-thread partial sums over the group (shuffles, then shared-memory atomics)
     // and add one value per channel to the global statistics.
+    // staging of the four warps' partial sums: [warp][a][scg][16] floats per group, in the coefficient
+    // cache (only BNBWD_APPLY uses that, and it takes no statistics)
+    float* my_red = reinterpret_cast<float*>(sCoef) + grp * 1024;
     auto flush_stats = [&](int n_tile) {
       if (!want_stats || n_tile < 0) return;
-      for (int i = et; i < 2 * kHalf * kCW; i += kEpiThreads) my_red[i] = 0.f;
-      named_bar_sync(bar_id, kEpiThreads);
+      // Every warp reduces its rows with shuffles and parks its per-channel sums in shared memory; after
+      // ONE barrier 2*kHalf*kCW/4 threads add the four warps' values and issue one red.global.add.v4.f32
+      // each.  (The first version zeroed a buffer, used shared-memory atomics and three barriers: 2 us of
+      // a 7 us CIFAR-sized kernel.  Adding every warp's sums straight to global memory removes the last
+      // barrier too but quadruples the global adds, which costs 2.7 us on a 128-tile, 64-channel layer.)
+      const int wq = (et >> 5);
 #pragma unroll
       for (int a = 0; a < kHalf; ++a) {
+        float r1[8], r2[8];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           float v1 = acc1[a][k], v2 = acc2[a][k];
@@ -521,35 +528,44 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
             v1 += __shfl_xor_sync(0xffffffffu, v1, o);
             v2 += __shfl_xor_sync(0xffffffffu, v2, o);
           }
-          if (lane < kNcg) {
-            atomicAdd(my_red + a * kCW + scg * 8 + k, v1);
-            atomicAdd(my_red + kHalf * kCW + a * kCW + scg * 8 + k, v2);
-          }
+          r1[k] = v1;
+          r2[k] = v2;
           acc1[a][k] = acc2[a][k] = 0.f;
         }
-      }
-      named_bar_sync(bar_id, kEpiThreads);
-      // four channels per reduction (red.global.add.v4.f32): on CIFAR-sized layers every CTA owns ONE
-      // tile, so all 2 x gridDim groups hit the same few addresses at the same moment and the flush
-      // was 2.2 us of a 7 us kernel - same-address atomics serialise in the L2
-      const bool vec_ok = ((reinterpret_cast<uintptr_t>(p.stats) | ((uintptr_t)p.stats_ld * 4)) & 15) == 0 &&
-                          (p.n_valid & 3) == 0;
-      for (int i = 4 * et; i < 2 * kHalf * kCW; i += 4 * kEpiThreads) {
-        const int which = i / (kHalf * kCW);
-        const int r = i - which * kHalf * kCW;
-        const int a = r / kCW;
-        const int j = C_::kChunks >= 2 ? a * 2 + grp : 0;
-        const int col = n_tile * BN + j * kCW + (r - a * kCW);
-        float* dst = p.stats + which * p.stats_ld + col;
-        if (vec_ok) {
-          if (col < p.n_valid) red_add_v4_f32(dst, my_red[i], my_red[i + 1], my_red[i + 2], my_red[i + 3]);
-        } else {
-#pragma unroll
-          for (int q = 0; q < 4; ++q)
-            if (col + q < p.n_valid) atomicAdd(dst + q, my_red[i + q]);
+        if (lane < kNcg) {   // lane == scg
+          float4* dst = reinterpret_cast<float4*>(my_red + ((wq * kHalf + a) * kNcg + scg) * 16);
+          dst[0] = make_float4(r1[0], r1[1], r1[2], r1[3]);
+          dst[1] = make_float4(r1[4], r1[5], r1[6], r1[7]);
+          dst[2] = make_float4(r2[0], r2[1], r2[2], r2[3]);
+          dst[3] = make_float4(r2[4], r2[5], r2[6], r2[7]);
         }
       }
       named_bar_sync(bar_id, kEpiThreads);
+      // (the buffer is not rewritten before every thread has passed at least one chunk barrier of the
+      //  next tile, which the adding threads below reach only after their reads)
+      const bool vec_ok = ((reinterpret_cast<uintptr_t>(p.stats) | ((uintptr_t)p.stats_ld * 4)) & 15) == 0;
+      if (et < kHalf * kNcg * 4) {
+        const int q = et & 3;               // which float4 of the 16: (sum | sum2) x (channels 0-3 | 4-7)
+        const int g8 = (et >> 2) % kNcg;    // 8-channel group
+        const int a = (et >> 2) / kNcg;
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int w = 0; w < kEpiThreads / 32; ++w) {
+          const float4 u = *reinterpret_cast<const float4*>(my_red + ((w * kHalf + a) * kNcg + g8) * 16 + q * 4);
+          t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+        }
+        const int j = C_::kChunks >= 2 ? a * 2 + grp : 0;
+        const int col = n_tile * BN + j * kCW + g8 * 8 + (q & 1) * 4;
+        float* dst = p.stats + (q >> 1) * p.stats_ld + col;
+        if (vec_ok && col + 4 <= p.n_valid) {
+          red_add_v4_f32(dst, t.x, t.y, t.z, t.w);
+        } else {
+          const float tv[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (col + k < p.n_valid) atomicAdd(dst + k, tv[k]);
+        }
+      }
     };
     // Side-input prefetch cursor (leader thread only): the group's chunks are requested strictly in
     // order, so (tile, chunk, column tile, row index, ring slot) advance incrementally - the leader
