@@ -64,7 +64,24 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 // kernel in the stream be scheduled as soon as every CTA of this grid has executed it or exited;
 // pdl_wait() blocks until all predecessor grids have completed and their writes are visible.
 // Both are no-ops when the kernel was launched without the attribute.
-__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;"); }
+// Two placements of the trigger (compile time, DRN_PDL_LATE): at the top of a kernel the dependent grid
+// becomes resident while this one still runs - its blocks then hold thread slots and shared memory that
+// the concurrent filter-gradient stream needs - so the default is LATE: a CTA triggers when it starts its
+// last piece of work (convolutions) or simply by exiting (element-wise kernels), and only the dependent's
+// launch latency and prologue overlap this grid's drain.
+#ifndef DRN_PDL_LATE
+#define DRN_PDL_LATE 1
+#endif
+__device__ __forceinline__ void pdl_trigger() {
+#if !DRN_PDL_LATE
+  asm volatile("griddepcontrol.launch_dependents;");
+#endif
+}
+__device__ __forceinline__ void pdl_trigger_late() {
+#if DRN_PDL_LATE
+  asm volatile("griddepcontrol.launch_dependents;");
+#endif
+}
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ bool elect_one() {

@@ -608,6 +608,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_consta
     uint32_t acc_phase = 0;
     int tile_iter = 0;
     for (int t = t_begin; t < t_end; ++t, ++tile_iter) {
+      if (t + 1 == t_end && threadIdx.x == 128) pdl_trigger_late();   // this CTA is on its last tile
       const bool my_tile = C_::kChunks >= 2 || (tile_iter & 1) == grp;
       if (my_tile) {
         const int n_tile = t / p.m_tiles;

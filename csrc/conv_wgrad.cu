@@ -311,6 +311,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmapDY, const __grid_const
       const int co = co_tile * 128 + row;
       mbar_wait(tfull_bar, 0, 0x140);
       tc_fence_after();
+      if (threadIdx.x == 64) pdl_trigger_late();   // only the split-K reduction is left
       // deterministic mode: the split-K partial tiles of one output tile are added in split order
       unsigned int* sem = (p.det_sem != nullptr && p.splits > 1) ? p.det_sem + blockIdx.x / p.splits : nullptr;
       if (sem != nullptr) {
